@@ -1,0 +1,257 @@
+/*
+ * kas_oracle.c -- CPU restatement of kiosk-autoscaler's tally/decision path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Built into oracle/libkas_oracle.so by
+ * oracle/build.py; loaded by tests/, __graft_entry__.smoke() and bench.py's
+ * CPU-baseline / --impl reference legs.  Nothing in the product library links
+ * or calls it.
+ *
+ * Citations are to the reference checkout (autoscaler/autoscaler.py unless
+ * stated).  The arithmetic follows oracle/oracle.py, which is the readable
+ * form; this file exists so that parity can be checked at sizes where Python
+ * loops are too slow, and so that the CPU baseline can use every host core.
+ *
+ * Parity status: decision math and LLEN term pinned by the reference's
+ * known-answer test (autoscaler_test.py:87-102) and by tests/golden/ (made by
+ * executing the reference's own source, oracle/make_golden.py).  SCAN MATCH
+ * term: PARITY UNPINNED upstream (glob runs in redis-server, version
+ * unpinned; no reference test creates a processing-* key); the matcher below
+ * restates the published Redis glob rules.
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#define KAS_EXPORT __attribute__((visibility("default")))
+
+/* ---- Redis glob (redis-server util.c stringmatchlen semantics) ---------- */
+static int glob_rec(const uint8_t *p, long pl, const uint8_t *s, long sl)
+{
+    while (pl > 0) {
+        uint8_t c = p[0];
+        if (c == '*') {
+            while (pl > 1 && p[1] == '*') { p++; pl--; }
+            if (pl == 1) return 1;
+            for (;;) {
+                if (glob_rec(p + 1, pl - 1, s, sl)) return 1;
+                if (sl == 0) return 0;
+                s++; sl--;
+            }
+        } else if (c == '?') {
+            if (sl == 0) return 0;
+            s++; sl--; p++; pl--;
+            continue;
+        } else if (c == '[') {
+            int neg, hit = 0;
+            if (sl == 0) return 0;
+            p++; pl--;
+            neg = (pl > 0 && p[0] == '^');
+            if (neg) { p++; pl--; }
+            for (;;) {
+                if (pl >= 2 && p[0] == '\\') {
+                    p++; pl--;
+                    if (p[0] == s[0]) hit = 1;
+                } else if (pl > 0 && p[0] == ']') {
+                    break;
+                } else if (pl <= 0) {
+                    p--; pl++;
+                    break;
+                } else if (pl >= 3 && p[1] == '-') {
+                    uint8_t lo = p[0], hi = p[2];
+                    if (lo > hi) { uint8_t t = lo; lo = hi; hi = t; }
+                    p += 2; pl -= 2;
+                    if (s[0] >= lo && s[0] <= hi) hit = 1;
+                } else {
+                    if (p[0] == s[0]) hit = 1;
+                }
+                p++; pl--;
+            }
+            if (neg) hit = !hit;
+            if (!hit) return 0;
+            s++; sl--; p++; pl--;
+            continue;
+        } else if (c == '\\' && pl >= 2) {
+            p++; pl--;
+            c = p[0];
+        }
+        if (sl == 0 || s[0] != c) return 0;
+        s++; sl--; p++; pl--;
+    }
+    return sl == 0;
+}
+
+KAS_EXPORT int kas_oracle_glob_match(const uint8_t *pat, uint32_t pat_len,
+                                     const uint8_t *str, uint32_t str_len)
+{
+    return glob_rec(pat, (long)pat_len, str, (long)str_len);
+}
+
+/* ---- SCAN term of tally_queues (autoscaler.py:69-71) --------------------
+ * One full pass over the keyspace PER QUEUE, like the reference: pattern
+ * "processing-" + q + ":*" (autoscaler.py:69) applied to every key.
+ * Keys are a blob + offsets (key i = blob[off[i] .. off[i+1])).             */
+KAS_EXPORT void kas_oracle_match_counts(const uint8_t *blob, const uint64_t *off,
+                                        uint64_t n_keys,
+                                        const uint8_t *names, const uint32_t *name_off,
+                                        uint32_t n_queues, uint64_t *counts,
+                                        int threads)
+{
+    for (uint32_t q = 0; q < n_queues; ++q) {
+        uint32_t nl = name_off[q + 1] - name_off[q];
+        uint32_t pl = 11 + nl + 2;
+        uint8_t *pat = (uint8_t *)malloc(pl);
+        memcpy(pat, "processing-", 11);
+        memcpy(pat + 11, names + name_off[q], nl);
+        pat[11 + nl] = ':';
+        pat[11 + nl + 1] = '*';
+        uint64_t c = 0;
+#pragma omp parallel for reduction(+:c) schedule(static) num_threads(threads > 0 ? threads : 1)
+        for (uint64_t i = 0; i < n_keys; ++i) {
+            c += (uint64_t)glob_rec(pat, pl, blob + off[i], (long)(off[i + 1] - off[i]));
+        }
+        counts[q] = c;
+        free(pat);
+    }
+}
+
+/* Same, over fixed-width records (each record scanned as a rec_bytes-long
+ * key).  For literal queue names a pattern "literal*" gives the same verdict
+ * on a zero-padded/truncated head as on the full key as long as the literal
+ * fits in the record and contains no NUL.                                   */
+KAS_EXPORT void kas_oracle_match_counts_heads(const uint8_t *heads, uint64_t n_keys,
+                                              uint32_t rec_bytes,
+                                              const uint8_t *names, const uint32_t *name_off,
+                                              uint32_t n_queues, uint64_t *counts,
+                                              int threads)
+{
+    for (uint32_t q = 0; q < n_queues; ++q) {
+        uint32_t nl = name_off[q + 1] - name_off[q];
+        uint32_t pl = 11 + nl + 2;
+        uint8_t *pat = (uint8_t *)malloc(pl);
+        memcpy(pat, "processing-", 11);
+        memcpy(pat + 11, names + name_off[q], nl);
+        pat[11 + nl] = ':';
+        pat[11 + nl + 1] = '*';
+        uint64_t c = 0;
+#pragma omp parallel for reduction(+:c) schedule(static) num_threads(threads > 0 ? threads : 1)
+        for (uint64_t i = 0; i < n_keys; ++i) {
+            c += (uint64_t)glob_rec(pat, pl, heads + i * rec_bytes, (long)rec_bytes);
+        }
+        counts[q] = c;
+        free(pat);
+    }
+}
+
+/* ---- Decision (autoscaler.py:197-219) ----------------------------------- */
+static inline int64_t floordiv64(int64_t a, int64_t b)
+{
+    int64_t q = a / b;
+    if ((a % b != 0) && ((a < 0) != (b < 0))) q -= 1;   /* Python // */
+    return q;
+}
+
+static inline int64_t clip64(int64_t d, int64_t mn, int64_t mx, int64_t cur)
+{
+    if (d > mx) d = mx;                 /* :200 */
+    else if (d < mn) d = mn;            /* :202 */
+    if (0 < d && d < cur) d = cur;      /* :207 */
+    return d;
+}
+
+KAS_EXPORT int64_t kas_oracle_clip_pod_count(int64_t desired, int64_t mn, int64_t mx, int64_t cur)
+{
+    return clip64(desired, mn, mx, cur);
+}
+
+/* kpp == 0 is the caller's problem (the reference raises ZeroDivisionError). */
+KAS_EXPORT int64_t kas_oracle_get_desired_pods(int64_t tally, int64_t kpp, int64_t mn,
+                                               int64_t mx, int64_t cur)
+{
+    return clip64(floordiv64(tally, kpp), mn, mx, cur);
+}
+
+/* ---- Replay over a trace (autoscaler.py:247-260 + :227-237) -------------
+ * llen [T][Q] tick-major.  inprog_mode 0: none, 1: [Q], 2: [T][Q].
+ * group_off NULL -> every queue is its own resource (R == Q).
+ * policies [S][3] = kpp, min, max.  Outputs [R][S].
+ * dense (optional) [S][T][R] int32 = replicas after each tick.              */
+KAS_EXPORT void kas_oracle_replay(const int32_t *llen, const int32_t *inprog, int inprog_mode,
+                                  uint32_t T, uint64_t Q,
+                                  const uint64_t *group_off, uint64_t R,
+                                  const int32_t *cur0,
+                                  const int32_t *policies, uint32_t S,
+                                  int64_t *pod_ticks, int64_t *n_patches, int32_t *final_cur,
+                                  int32_t *dense, int threads)
+{
+#pragma omp parallel for schedule(static) num_threads(threads > 0 ? threads : 1)
+    for (uint64_t r = 0; r < R; ++r) {
+        uint64_t q0 = group_off ? group_off[r] : r;
+        uint64_t q1 = group_off ? group_off[r + 1] : r + 1;
+        for (uint32_t s = 0; s < S; ++s) {
+            int64_t kpp = policies[3 * s], mn = policies[3 * s + 1], mx = policies[3 * s + 2];
+            int64_t cur = cur0 ? cur0[r] : 0;
+            int64_t pt = 0, np = 0;
+            for (uint32_t t = 0; t < T; ++t) {
+                int64_t sum = 0;
+                for (uint64_t q = q0; q < q1; ++q) {
+                    int64_t tally = llen[(uint64_t)t * Q + q];
+                    if (inprog_mode == 1) tally += inprog[q];
+                    else if (inprog_mode == 2) tally += inprog[(uint64_t)t * Q + q];
+                    sum += clip64(floordiv64(tally, kpp), mn, mx, cur);   /* :255-257 */
+                }
+                int64_t desired = clip64(sum, mn, mx, cur);               /* :259 */
+                if (desired != cur) { np += 1; cur = desired; }           /* :227 */
+                pt += cur;
+                if (dense) dense[((uint64_t)s * T + t) * R + r] = (int32_t)cur;
+            }
+            pod_ticks[r * S + s] = pt;
+            n_patches[r * S + s] = np;
+            final_cur[r * S + s] = (int32_t)cur;
+        }
+    }
+}
+
+/* ---- Twin of the library's synthetic trace generator --------------------
+ * (restated from the written spec in DESIGN.md, used to rebuild any sampled
+ * queue's full trajectory when the trace only exists in HBM).               */
+static inline uint64_t mix64(uint64_t z)
+{
+    z += 0x9E3779B97F4A7C15ULL;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
+}
+
+KAS_EXPORT int32_t kas_oracle_trace_value(uint64_t seed, uint64_t q, uint32_t t)
+{
+    uint64_t epoch = t >> 6;
+    uint64_t he = mix64(mix64(seed ^ (q * 0xD1342543DE82EF95ULL)) + epoch);
+    uint64_t ht = mix64(he ^ ((uint64_t)t * 0x2545F4914F6CDD1DULL));
+    uint32_t active = (uint32_t)(he % 100u) < 45u;
+    uint32_t level = (uint32_t)((he >> 8) % 400u);
+    uint32_t jitter = (uint32_t)(ht & 0xFFu);
+    if (active) return (int32_t)((level * jitter) >> 7);
+    if (jitter < 10u) return (int32_t)((ht >> 8) & 3u);
+    return 0;
+}
+
+KAS_EXPORT void kas_oracle_trace_fill(uint64_t seed, uint32_t T, uint64_t q_first,
+                                      uint64_t n_q, int32_t *out /* [T][n_q] */, int threads)
+{
+#pragma omp parallel for schedule(static) num_threads(threads > 0 ? threads : 1)
+    for (uint32_t t = 0; t < T; ++t)
+        for (uint64_t j = 0; j < n_q; ++j)
+            out[(uint64_t)t * n_q + j] = kas_oracle_trace_value(seed, q_first + j, t);
+}
+
+KAS_EXPORT int kas_oracle_max_threads(void)
+{
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
