@@ -1,0 +1,225 @@
+/*
+ * kas.h -- C ABI of libkas.so: the B200 (sm_100a) implementation of
+ * kiosk-autoscaler's queue tally and replica decision, batched over a packed
+ * keyspace snapshot and a queue-depth trace.
+ *
+ * The reference has no FFI; its boundary is the Python object API
+ * (autoscaler/__init__.py:30-32).  This header is what the drop-in Python
+ * package (kiosk-autoscaler_b200/autoscaler) binds with ctypes; every entry
+ * point names the reference lines whose work it takes over.  Paths are
+ * relative to the reference checkout; "autoscaler.py" means
+ * autoscaler/autoscaler.py.
+ *
+ * Conventions
+ *   - plain C types, no torch / C++ types; return 0 (KAS_OK) or a negative
+ *     kas_status; nothing throws across the boundary.
+ *   - the CALLER owns every device buffer ("d_" prefix) and every host buffer;
+ *     the library allocates no device memory and keeps no global mutable state
+ *     besides a per-thread copy of the last CUDA error string.
+ *   - all device work is enqueued on the given stream and is asynchronous with
+ *     respect to the host; `stream` is a cudaStream_t passed as void*.
+ *   - integer results are bit-exact with the reference's Python arithmetic
+ *     inside the stated domains; outside them the call is rejected, never
+ *     approximated.  There is no CPU fallback: without a CUDA device every
+ *     entry point that launches work returns KAS_ERR_CUDA.
+ */
+#ifndef KAS_H_
+#define KAS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KAS_VERSION 100 /* 0.1.0 */
+
+#if defined(__GNUC__)
+#define KAS_API __attribute__((visibility("default")))
+#else
+#define KAS_API
+#endif
+
+typedef enum kas_status {
+    KAS_OK = 0,
+    KAS_ERR_INVALID = -1,       /* null pointer, bad size, bad flag            */
+    KAS_ERR_UNSUPPORTED = -2,   /* outside the accelerated domain (see call)    */
+    KAS_ERR_CUDA = -3,          /* a CUDA call failed; see kas_last_cuda_error  */
+    KAS_ERR_ALIGNMENT = -4,     /* device pointer not aligned as required       */
+    KAS_ERR_ZERO_DIVISION = -5, /* keys_per_pod == 0 (reference: ZeroDivisionError,
+                                   autoscaler.py:217)                           */
+    KAS_ERR_GLOB_META = -6,     /* queue name holds * ? [ \ : a live glob in the
+                                   reference (autoscaler.py:69); use
+                                   kas_glob_count                                */
+    KAS_ERR_TOO_SMALL = -7      /* caller's output buffer is too small          */
+} kas_status;
+
+KAS_API int kas_version(void);
+KAS_API const char *kas_strerror(int status);
+/* Text of the last CUDA error seen by the calling thread ("" if none). */
+KAS_API const char *kas_last_cuda_error(void);
+/* SM count and compute capability of the current device. */
+KAS_API int kas_device_info(int *sm_count, int *cc_major, int *cc_minor);
+
+/* ------------------------------------------------------------------------
+ * Key-snapshot ingest: variable-length keys -> fixed-width "heads".
+ * Replaces the client side of SCAN iteration (autoscaler.py:70-71, which
+ * pulls every key over TCP once per queue): the keyspace is taken once and
+ * the first rec_bytes bytes of every key are stored zero-padded, rec_bytes a
+ * multiple of 16, records contiguous, so the match kernel streams them.
+ * ---------------------------------------------------------------------- */
+
+/* Smallest record width (multiple of 16) that holds "processing-" + name + ":"
+ * for a name of max_name_len bytes (autoscaler.py:69). */
+KAS_API uint32_t kas_rec_bytes_for(uint32_t max_name_len);
+
+/* Host packer.  Key i is blob[off[i] .. off[i+1]-sep_bytes): sep_bytes is 0 for
+ * a plain blob+offsets store and 1 for a newline-separated dump indexed by
+ * kas_index_lines_host.  out is n_keys*rec_bytes. */
+KAS_API int kas_pack_heads_host(const uint8_t *blob, const uint64_t *off, uint64_t n_keys,
+                        uint32_t sep_bytes, uint32_t rec_bytes, uint8_t *out, int threads);
+
+/* Index a newline-separated key dump (`redis-cli --scan` output): off[i] is the
+ * start of line i, and one more entry closes the last line (blob_len+1 when the
+ * dump does not end in '\n', as if it did), so key i is
+ * blob[off[i] .. off[i+1]-1) -- pack with sep_bytes = 1.  *n_keys gets the
+ * count.  A trailing '\r' is not stripped (keys are binary-safe bytes).  off
+ * may be NULL to count only; off_cap is its capacity in elements
+ * (KAS_ERR_TOO_SMALL if n_keys+1 does not fit). */
+KAS_API int kas_index_lines_host(const uint8_t *blob, uint64_t blob_len, uint64_t *off,
+                         uint64_t off_cap, uint64_t *n_keys);
+
+/* Device packer for a blob already resident in HBM.  d_heads must be 16-byte
+ * aligned.  Reads every key's first min(len, rec_bytes) bytes. */
+KAS_API int kas_pack_heads(const uint8_t *d_blob, const uint64_t *d_off, uint64_t n_keys,
+                   uint32_t sep_bytes, uint32_t rec_bytes, uint8_t *d_heads, void *stream);
+
+/* ------------------------------------------------------------------------
+ * Queue-prefix table.  Built on the host from the queue names held by
+ * Autoscaler.redis_keys (autoscaler.py:52), copied to the device by the
+ * caller, staged in shared memory by the match kernel.
+ * Names must be unique, free of NUL and of the glob metacharacters * ? [ \
+ * (KAS_ERR_GLOB_META otherwise), at most rec_bytes-12 bytes long, and at most
+ * KAS_MAX_PREFIXES of them.
+ * ---------------------------------------------------------------------- */
+#define KAS_MAX_PREFIXES 1024u
+#define KAS_MAX_REC_BYTES 64u
+
+KAS_API size_t kas_prefix_table_bytes(uint32_t n_prefix, uint32_t rec_bytes);
+/* names: concatenated name bytes; name q is names[name_off[q] .. name_off[q+1]). */
+KAS_API int kas_prefix_table_build(const uint8_t *names, const uint32_t *name_off, uint32_t n_prefix,
+                           uint32_t rec_bytes, void *host_tbl, size_t tbl_bytes);
+
+/* ------------------------------------------------------------------------
+ * K1: prefix match and count.
+ * Replaces, for all queues in ONE pass over the keyspace,
+ *     scan = redis_client.scan_iter(match='processing-{}:*'.format(q), count=1000)
+ *     num_in_progress = len([x for x in scan])          (autoscaler.py:69-71)
+ * d_counts[q] = number of records that start with "processing-" + name_q + ":".
+ * Every queue is counted independently, so a key counts for several queues
+ * when one such prefix is a prefix of another (as in the reference, where
+ * every queue runs its own SCAN).  No dedup (autoscaler.py:71).
+ * d_heads: n_keys records of rec_bytes, 16-byte aligned.  d_counts: uint64
+ * [n_prefix].  kas_match_count overwrites d_counts; kas_match_count_accumulate
+ * adds to it (for snapshots streamed through HBM in chunks).
+ * ---------------------------------------------------------------------- */
+KAS_API int kas_match_count(const void *d_heads, uint64_t n_keys, uint32_t rec_bytes,
+                    const void *d_prefix_tbl, uint32_t n_prefix, uint64_t *d_counts,
+                    void *stream);
+KAS_API int kas_match_count_accumulate(const void *d_heads, uint64_t n_keys, uint32_t rec_bytes,
+                               const void *d_prefix_tbl, uint32_t n_prefix, uint64_t *d_counts,
+                               void *stream);
+
+/* ------------------------------------------------------------------------
+ * Element-wise decision, the scalar API's arithmetic.
+ * mode 0: out[i] = clip_pod_count(a[i] // kpp[i], mn[i], mx[i], cur[i])
+ *         = Autoscaler.get_desired_pods with redis_keys[key] == a[i]
+ *           (autoscaler.py:215-219); Python floor division; any kpp[i] == 0
+ *           -> the whole call is rejected with KAS_ERR_ZERO_DIVISION and
+ *           d_status (int32[1], device) is set to 1.
+ * mode 1: out[i] = Autoscaler.clip_pod_count(a[i], mn[i], mx[i], cur[i])
+ *           (autoscaler.py:197-213); d_kpp is ignored and may be NULL.
+ * All arrays int64 [n] on the device.  Domain: every int64 value.
+ * The zero-divisor check runs on the device; read d_status after syncing.
+ * ---------------------------------------------------------------------- */
+KAS_API int kas_decide(const int64_t *d_a, const int64_t *d_kpp, const int64_t *d_mn,
+               const int64_t *d_mx, const int64_t *d_cur, uint64_t n, int mode,
+               int64_t *d_out, int32_t *d_status, void *stream);
+
+/* ------------------------------------------------------------------------
+ * K2: fused tally + desired pods + clamp + hysteresis replay over a trace.
+ * Replaces T iterations of Autoscaler.scale for R resources and S policies
+ * (autoscaler.py:244-260), with a well-behaved cluster standing in for
+ * get_current_pods / scale_resource: what tick t patches is what tick t+1
+ * reads (autoscaler.py:179,189 <- :232,236), no patch when nothing changes
+ * (:227-228).  Per tick and resource r with queues q in
+ * [group_off[r], group_off[r+1]):
+ *     tally_q  = llen[t][q] + inprog(t,q)                     (:73)
+ *     d_q      = clip(tally_q // kpp, min, max, cur)          (:215-219)
+ *     desired  = clip(sum_q d_q, min, max, cur)               (:254-260)
+ *     n_patches += desired != cur;  cur = desired             (:227-237)
+ *     pod_ticks += cur
+ * ---------------------------------------------------------------------- */
+typedef struct kas_policy {
+    int32_t keys_per_pod; /* KEYS_PER_POD, scale.py:92; != 0, may be negative  */
+    int32_t min_pods;     /* MIN_PODS,     scale.py:90                          */
+    int32_t max_pods;     /* MAX_PODS,     scale.py:91                          */
+} kas_policy;
+
+typedef struct kas_totals {
+    int64_t pod_ticks;     /* sum over ticks of replicas after the tick         */
+    uint32_t n_patches;    /* ticks on which scale_resource would have patched  */
+    int32_t final_current; /* replicas after the last tick                      */
+} kas_totals;
+
+typedef struct kas_replay_args {
+    const int32_t *d_llen;      /* [T][Q] tick-major LLEN trace (autoscaler.py:67) */
+    const int32_t *d_inprog;    /* SCAN-count term: NULL, [Q] or [T][Q]            */
+    int32_t inprog_mode;        /* 0 none, 1 per queue [Q], 2 per tick [T][Q]      */
+    uint32_t n_ticks;           /* T                                               */
+    uint64_t n_queues;          /* Q                                               */
+    uint64_t n_resources;       /* R (== Q when d_group_off is NULL)               */
+    const uint64_t *d_group_off;/* [R+1] CSR offsets into the queue axis, or NULL  */
+    const int32_t *d_cur0;      /* [R] replicas before tick 0, or NULL for zeros   */
+    const kas_policy *policies; /* HOST pointer, [S]                               */
+    uint32_t n_policies;        /* S                                               */
+    kas_totals *d_totals;       /* [R][S] out, or NULL                             */
+    int64_t *d_sums;            /* [S][3] out: sum over resources of pod_ticks,
+                                   n_patches, final_current (what the box-wide
+                                   allreduce carries), or NULL                     */
+    int32_t *d_dense;           /* [S][T][R] replicas after each tick, or NULL     */
+} kas_replay_args;
+
+/* Domain: trace values and cur0 any int32; policies any int32 with
+ * keys_per_pod != 0 (KAS_ERR_ZERO_DIVISION otherwise, nothing is launched).
+ * d_llen / d_inprog / d_dense need 4-byte alignment; 16-byte alignment and
+ * Q % 4 == 0 enable the vectorised path for single-queue resources.        */
+KAS_API int kas_replay(const kas_replay_args *args, void *stream);
+
+/* ------------------------------------------------------------------------
+ * Synthetic workload generators (no counterpart in the reference, which has
+ * no benchmark; used by bench.py and the tests; specified in DESIGN.md so the
+ * oracle can rebuild any element independently).
+ * ---------------------------------------------------------------------- */
+/* d_out[t][j] = f(seed, q_first + j, t), int32 [T][n_q], tick-major. */
+KAS_API int kas_synth_trace(uint64_t seed, uint32_t n_ticks, uint64_t q_first, uint64_t n_q,
+                    int32_t *d_out, void *stream);
+
+/* Host: write synthetic keys first_key .. first_key+n_keys-1 as packed heads
+ * (out_heads, n_keys*rec_bytes, may be NULL) and/or as a blob with offsets
+ * (out_blob/out_off, may be NULL; out_off has n_keys+1 entries; blob_cap is
+ * the capacity of out_blob; *blob_len gets the bytes needed/written).
+ * About half of the keys are "processing-<name>:<suffix>" for one of the
+ * given names; the rest are near misses.  long_tail != 0 gives a long-tailed
+ * length distribution (keys up to ~700 bytes). */
+KAS_API int kas_synth_keys_host(uint64_t seed, uint64_t first_key, uint64_t n_keys,
+                        const uint8_t *names, const uint32_t *name_off, uint32_t n_names,
+                        int long_tail, uint32_t rec_bytes, uint8_t *out_heads,
+                        uint8_t *out_blob, uint64_t blob_cap, uint64_t *out_off,
+                        uint64_t *blob_len, int threads);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KAS_H_ */

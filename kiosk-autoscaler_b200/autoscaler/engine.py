@@ -1,0 +1,374 @@
+"""ctypes binding of libkas.so (include/kas.h) plus the buffer hand-off.
+
+PyTorch is used for exactly three things: allocating device / pinned buffers,
+``.data_ptr()``, and the current CUDA stream.  All arithmetic of the tally and
+decision path happens in the library's sm_100a kernels; there is no CPU
+fallback -- if the library is missing or no CUDA device is present every call
+raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+import numpy as np
+
+KAS_OK = 0
+KAS_ERR_INVALID = -1
+KAS_ERR_UNSUPPORTED = -2
+KAS_ERR_CUDA = -3
+KAS_ERR_ALIGNMENT = -4
+KAS_ERR_ZERO_DIVISION = -5
+KAS_ERR_GLOB_META = -6
+KAS_ERR_TOO_SMALL = -7
+
+MAX_PREFIXES = 1024
+MAX_REC_BYTES = 64
+LITERAL = b'processing-'          # autoscaler.py:69 of the reference
+GLOB_META = frozenset(b'*?[\\')
+
+_PKG_DIR = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB_PATH = os.environ.get('KAS_LIB', os.path.join(_PKG_DIR, 'lib', 'libkas.so'))
+
+
+class KasError(RuntimeError):
+    """A libkas call returned a negative status."""
+
+    def __init__(self, status, what, detail=''):
+        self.status = status
+        msg = '%s failed: %s' % (what, _strerror(status))
+        if detail:
+            msg += ' [%s]' % detail
+        super().__init__(msg)
+
+
+class GlobQueueNameError(NotImplementedError):
+    """A queue name holds a glob metacharacter; in the reference such a name is
+    a live glob (autoscaler.py:69) and needs the general glob kernel."""
+
+
+class Policy(C.Structure):
+    _fields_ = [('keys_per_pod', C.c_int32), ('min_pods', C.c_int32), ('max_pods', C.c_int32)]
+
+
+class Totals(C.Structure):
+    _fields_ = [('pod_ticks', C.c_int64), ('n_patches', C.c_uint32), ('final_current', C.c_int32)]
+
+
+TOTALS_DTYPE = np.dtype([('pod_ticks', '<i8'), ('n_patches', '<u4'), ('final_current', '<i4')])
+
+
+class ReplayArgs(C.Structure):
+    _fields_ = [('d_llen', C.c_void_p), ('d_inprog', C.c_void_p), ('inprog_mode', C.c_int32),
+                ('n_ticks', C.c_uint32), ('n_queues', C.c_uint64), ('n_resources', C.c_uint64),
+                ('d_group_off', C.c_void_p), ('d_cur0', C.c_void_p),
+                ('policies', C.POINTER(Policy)), ('n_policies', C.c_uint32),
+                ('d_totals', C.c_void_p), ('d_sums', C.c_void_p), ('d_dense', C.c_void_p)]
+
+
+_lib = None
+_lib_lock = threading.Lock()
+
+# name -> (restype, argtypes); every symbol include/kas.h declares.
+SYMBOLS = {
+    'kas_version': (C.c_int, []),
+    'kas_strerror': (C.c_char_p, [C.c_int]),
+    'kas_last_cuda_error': (C.c_char_p, []),
+    'kas_device_info': (C.c_int, [C.POINTER(C.c_int)] * 3),
+    'kas_rec_bytes_for': (C.c_uint32, [C.c_uint32]),
+    'kas_pack_heads_host': (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32,
+                                      C.c_void_p, C.c_int]),
+    'kas_index_lines_host': (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
+                                       C.POINTER(C.c_uint64)]),
+    'kas_pack_heads': (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32,
+                                 C.c_void_p, C.c_void_p]),
+    'kas_prefix_table_bytes': (C.c_size_t, [C.c_uint32, C.c_uint32]),
+    'kas_prefix_table_build': (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32,
+                                         C.c_void_p, C.c_size_t]),
+    'kas_match_count': (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_uint32,
+                                  C.c_void_p, C.c_void_p]),
+    'kas_match_count_accumulate': (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p,
+                                             C.c_uint32, C.c_void_p, C.c_void_p]),
+    'kas_decide': (C.c_int, [C.c_void_p] * 5 + [C.c_uint64, C.c_int, C.c_void_p, C.c_void_p,
+                                                C.c_void_p]),
+    'kas_replay': (C.c_int, [C.POINTER(ReplayArgs), C.c_void_p]),
+    'kas_synth_trace': (C.c_int, [C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint64, C.c_void_p,
+                                  C.c_void_p]),
+    'kas_synth_keys_host': (C.c_int, [C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p,
+                                      C.c_uint32, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p,
+                                      C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64), C.c_int]),
+}
+
+
+def lib():
+    """Load libkas.so once.  Raises if it has not been built: the GPU path is
+    the only path."""
+    global _lib
+    if _lib is None:
+        with _lib_lock:
+            if _lib is None:
+                if not os.path.exists(LIB_PATH):
+                    raise ImportError(
+                        'libkas.so not found at %s -- build it with '
+                        '`python kiosk-autoscaler_b200/build.py`; there is no CPU fallback'
+                        % LIB_PATH)
+                L = C.CDLL(LIB_PATH)
+                for name, (res, args) in SYMBOLS.items():
+                    fn = getattr(L, name)
+                    fn.restype = res
+                    fn.argtypes = args
+                _lib = L
+    return _lib
+
+
+def _strerror(status):
+    try:
+        return lib().kas_strerror(status).decode()
+    except Exception:  # pragma: no cover - library missing
+        return 'status %d' % status
+
+
+def check(status, what):
+    if status == KAS_OK:
+        return
+    if status == KAS_ERR_ZERO_DIVISION:
+        # same exception type and text as `x // 0` in the reference (autoscaler.py:217)
+        raise ZeroDivisionError('integer division or modulo by zero')
+    if status == KAS_ERR_GLOB_META:
+        raise GlobQueueNameError(
+            '%s: queue names containing * ? [ \\ are globs in the reference '
+            '(autoscaler.py:69) and are not handled by the prefix kernel' % what)
+    detail = lib().kas_last_cuda_error().decode() if status == KAS_ERR_CUDA else ''
+    raise KasError(status, what, detail)
+
+
+def _torch():
+    import torch
+    return torch
+
+
+def require_cuda():
+    torch = _torch()
+    if not torch.cuda.is_available():
+        raise RuntimeError('no CUDA device: the tally/decision path runs on the GPU only '
+                           '(there is no CPU fallback)')
+    return torch
+
+
+def stream_ptr():
+    return C.c_void_p(_torch().cuda.current_stream().cuda_stream)
+
+
+def ptr(t):
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def np_ptr(a):
+    return C.c_void_p(0 if a is None else a.ctypes.data)
+
+
+def encode_name(q):
+    return q if isinstance(q, (bytes, bytearray)) else str(q).encode('utf-8')
+
+
+def names_blob(names):
+    enc = [bytes(encode_name(q)) for q in names]
+    off = np.zeros(len(enc) + 1, dtype=np.uint32)
+    if enc:
+        off[1:] = np.cumsum([len(e) for e in enc])
+    blob = np.frombuffer(b''.join(enc) + b'\0', dtype=np.uint8).copy()
+    return blob, off
+
+
+def rec_bytes_for(names):
+    longest = max((len(encode_name(q)) for q in names), default=0)
+    return int(lib().kas_rec_bytes_for(longest))
+
+
+def host_threads():
+    return max(1, min(32, os.cpu_count() or 1))
+
+
+# --------------------------------------------------------------------------
+# host-side helpers (no GPU needed)
+# --------------------------------------------------------------------------
+def build_prefix_table(names, rec_bytes):
+    """Host image of the queue-prefix table (uint8 numpy array)."""
+    names = list(names)
+    if len(names) == 0 or len(names) > MAX_PREFIXES:
+        raise ValueError('between 1 and %d queue names are supported, got %d'
+                         % (MAX_PREFIXES, len(names)))
+    nbytes = lib().kas_prefix_table_bytes(len(names), rec_bytes)
+    if nbytes == 0:
+        raise KasError(KAS_ERR_UNSUPPORTED, 'kas_prefix_table_bytes')
+    blob, off = names_blob(names)
+    tbl = np.zeros(nbytes, dtype=np.uint8)
+    check(lib().kas_prefix_table_build(np_ptr(blob), np_ptr(off), len(names), rec_bytes,
+                                       np_ptr(tbl), nbytes), 'kas_prefix_table_build')
+    return tbl
+
+
+def pack_heads_host(blob, off, rec_bytes, out=None, sep_bytes=0, threads=None):
+    """blob+offsets -> uint8 [n][rec_bytes] (numpy, or written into `out`)."""
+    blob = np.ascontiguousarray(blob, dtype=np.uint8)
+    off = np.ascontiguousarray(off, dtype=np.uint64)
+    n = len(off) - 1
+    if out is None:
+        out = np.empty((n, rec_bytes), dtype=np.uint8)
+    check(lib().kas_pack_heads_host(np_ptr(blob), np_ptr(off), n, sep_bytes, rec_bytes,
+                                    C.c_void_p(out.ctypes.data if isinstance(out, np.ndarray)
+                                               else out.data_ptr()),
+                                    threads or host_threads()), 'kas_pack_heads_host')
+    return out
+
+
+def index_lines_host(blob):
+    blob = np.ascontiguousarray(blob, dtype=np.uint8)
+    n = C.c_uint64(0)
+    check(lib().kas_index_lines_host(np_ptr(blob), blob.size, None, 0, C.byref(n)),
+          'kas_index_lines_host')
+    off = np.empty(n.value + 1, dtype=np.uint64)
+    check(lib().kas_index_lines_host(np_ptr(blob), blob.size, np_ptr(off), off.size, C.byref(n)),
+          'kas_index_lines_host')
+    return off
+
+
+def synth_keys_host(seed, first_key, n_keys, names, long_tail=False, rec_bytes=0,
+                    want_heads=True, want_blob=False, heads_out=None, threads=None):
+    """Synthetic keyspace (spec in DESIGN.md).  Returns (heads|None, blob|None, off|None)."""
+    nblob, noff = names_blob(names)
+    threads = threads or host_threads()
+    heads = None
+    if want_heads:
+        heads = heads_out if heads_out is not None else np.empty((n_keys, rec_bytes), dtype=np.uint8)
+    hp = C.c_void_p(0) if heads is None else C.c_void_p(
+        heads.ctypes.data if isinstance(heads, np.ndarray) else heads.data_ptr())
+    blob = off = None
+    if want_blob:
+        need = C.c_uint64(0)
+        check(lib().kas_synth_keys_host(seed, first_key, n_keys, np_ptr(nblob), np_ptr(noff),
+                                        len(names), int(long_tail), rec_bytes, None, None, 0, None,
+                                        C.byref(need), threads), 'kas_synth_keys_host')
+        blob = np.empty(max(1, need.value), dtype=np.uint8)
+        off = np.empty(n_keys + 1, dtype=np.uint64)
+        check(lib().kas_synth_keys_host(seed, first_key, n_keys, np_ptr(nblob), np_ptr(noff),
+                                        len(names), int(long_tail), rec_bytes, hp, np_ptr(blob),
+                                        blob.size, np_ptr(off), C.byref(need), threads),
+              'kas_synth_keys_host')
+        blob = blob[:need.value]
+    elif want_heads:
+        check(lib().kas_synth_keys_host(seed, first_key, n_keys, np_ptr(nblob), np_ptr(noff),
+                                        len(names), int(long_tail), rec_bytes, hp, None, 0, None,
+                                        None, threads), 'kas_synth_keys_host')
+    return heads, blob, off
+
+
+# --------------------------------------------------------------------------
+# device calls
+# --------------------------------------------------------------------------
+POISON = np.uint64(0xFFFFFFFFFFFFFFFF)
+
+
+def match_count(d_heads, n_keys, rec_bytes, d_table, n_prefix, d_counts=None, accumulate=False):
+    """K1 on device tensors.  Returns the uint64 counts as an int64-typed CUDA
+    tensor of length n_prefix (not synchronised)."""
+    torch = require_cuda()
+    if d_counts is None:
+        d_counts = torch.empty(n_prefix, dtype=torch.int64, device=d_table.device)
+        accumulate = False
+    fn = lib().kas_match_count_accumulate if accumulate else lib().kas_match_count
+    check(fn(ptr(d_heads), n_keys, rec_bytes, ptr(d_table), n_prefix, ptr(d_counts), stream_ptr()),
+          'kas_match_count')
+    return d_counts
+
+
+def counts_to_host(d_counts):
+    """Synchronising read of K1's result; detects the table-mismatch poison."""
+    out = d_counts.cpu().numpy().view(np.uint64)
+    if out.size and (out == POISON).all():
+        raise KasError(KAS_ERR_INVALID, 'kas_match_count',
+                       'prefix table image does not match n_prefix/rec_bytes')
+    return out
+
+
+def decide(a, kpp, mn, mx, cur, mode=0):
+    """Element-wise get_desired_pods (mode 0) / clip_pod_count (mode 1) on the GPU.
+    Arguments are sequences of Python ints of equal length; returns list of int."""
+    torch = require_cuda()
+    n = len(a)
+    cols = [a, kpp if mode == 0 else [1] * n, mn, mx, cur]
+    try:
+        host = np.array(cols, dtype=np.int64)
+    except OverflowError as e:
+        raise OverflowError('pod counts and tallies must fit in a signed 64-bit integer') from e
+    dev = torch.from_numpy(host).to('cuda', non_blocking=False)
+    out = torch.empty(n, dtype=torch.int64, device='cuda')
+    status = torch.zeros(1, dtype=torch.int32, device='cuda')
+    check(lib().kas_decide(ptr(dev[0]), ptr(dev[1]), ptr(dev[2]), ptr(dev[3]), ptr(dev[4]), n,
+                           mode, ptr(out), ptr(status), stream_ptr()), 'kas_decide')
+    res = out.cpu()
+    if int(status.cpu()[0]) != 0:
+        check(KAS_ERR_ZERO_DIVISION, 'kas_decide')
+    return [int(v) for v in res.tolist()]
+
+
+def replay(d_llen, n_ticks, n_queues, policies, d_inprog=None, inprog_mode=0, d_group_off=None,
+           n_resources=None, d_cur0=None, want_totals=True, want_sums=True, want_dense=False):
+    """K2 on device tensors.  policies: sequence of (kpp, min, max).
+    Returns dict of CUDA tensors: totals (uint8 view [R][S][16]), sums int64 [S][3],
+    dense int32 [S][T][R] (those requested)."""
+    torch = require_cuda()
+    pol = [(int(k), int(a), int(b)) for (k, a, b) in policies]
+    for tup in pol:
+        for v in tup:
+            if not -(2 ** 31) <= v < 2 ** 31:
+                raise OverflowError('policy values must fit in int32, got %r' % (tup,))
+    S = len(pol)
+    R = n_queues if n_resources is None else n_resources
+    parr = (Policy * S)(*[Policy(*p) for p in pol])
+    dev = d_llen.device
+    out = {}
+    totals = torch.empty((R, S, 16), dtype=torch.uint8, device=dev) if want_totals else None
+    sums = torch.empty((S, 3), dtype=torch.int64, device=dev) if want_sums else None
+    dense = torch.empty((S, n_ticks, R), dtype=torch.int32, device=dev) if want_dense else None
+    args = ReplayArgs(ptr(d_llen), ptr(d_inprog), inprog_mode, n_ticks, n_queues, R,
+                      ptr(d_group_off), ptr(d_cur0), parr, S, ptr(totals), ptr(sums), ptr(dense))
+    check(lib().kas_replay(C.byref(args), stream_ptr()), 'kas_replay')
+    if want_totals:
+        out['totals'] = totals
+    if want_sums:
+        out['sums'] = sums
+    if want_dense:
+        out['dense'] = dense
+    return out
+
+
+def totals_to_host(d_totals):
+    """uint8 [R][S][16] CUDA tensor -> numpy structured array [R][S]."""
+    a = d_totals.cpu().numpy()
+    return a.reshape(a.shape[0], a.shape[1] * 16).view(TOTALS_DTYPE).reshape(a.shape[0], a.shape[1])
+
+
+def synth_trace(seed, n_ticks, q_first, n_q, device='cuda', out=None):
+    torch = require_cuda()
+    if out is None:
+        out = torch.empty((n_ticks, n_q), dtype=torch.int32, device=device)
+    check(lib().kas_synth_trace(seed, n_ticks, q_first, n_q, ptr(out), stream_ptr()),
+          'kas_synth_trace')
+    return out
+
+
+def pack_heads_device(d_blob, d_off, n_keys, rec_bytes, sep_bytes=0):
+    torch = require_cuda()
+    heads = torch.empty((n_keys, rec_bytes), dtype=torch.uint8, device=d_blob.device)
+    check(lib().kas_pack_heads(ptr(d_blob), ptr(d_off), n_keys, sep_bytes, rec_bytes, ptr(heads),
+                               stream_ptr()), 'kas_pack_heads')
+    return heads
+
+
+def device_info():
+    require_cuda()
+    a, b, c = C.c_int(0), C.c_int(0), C.c_int(0)
+    check(lib().kas_device_info(C.byref(a), C.byref(b), C.byref(c)), 'kas_device_info')
+    return dict(sm_count=a.value, cc=(b.value, c.value))

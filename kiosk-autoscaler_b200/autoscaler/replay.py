@@ -1,0 +1,157 @@
+"""Offline replay of the scale loop over a queue-depth trace (K2) and the
+sharding of keys / resources over the GPUs of one box.
+
+One tick of the reference is ``Autoscaler.scale`` (autoscaler.py:244-273 of the
+reference): tally, read current pods, sum of per-queue decisions, clip, patch.
+With a cluster that applies every patch, the replicas after tick t are the
+current pods of tick t+1, so a resource is a sequential recurrence over ticks
+while resources (and policies) are independent -- that is what is sharded.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from autoscaler import engine
+
+RESOURCE_FIELD = {'deployment': 'replicas', 'job': 'parallelism'}   # autoscaler.py:232,236
+
+
+class ReplayResult(object):
+    """Per (resource, policy) reductions of a replay, on the host.
+
+    pod_ticks[r][s]  sum over ticks of the replicas after the tick
+    n_patches[r][s]  ticks on which scale_resource would have patched
+    final[r][s]      replicas after the last tick
+    sums[s]          (sum_r pod_ticks, sum_r n_patches, sum_r final)
+    dense[s][t][r]   replicas after each tick (only when requested)
+    """
+
+    def __init__(self, policies, totals=None, sums=None, dense=None, n_ticks=0):
+        self.policies = [tuple(int(v) for v in p) for p in policies]
+        self.n_ticks = n_ticks
+        self.pod_ticks = self.n_patches = self.final = None
+        if totals is not None:
+            self.pod_ticks = totals['pod_ticks'].astype(np.int64)
+            self.n_patches = totals['n_patches'].astype(np.int64)
+            self.final = totals['final_current'].astype(np.int64)
+        self.sums = sums
+        self.dense = dense
+        self._cur0 = None
+
+    def pod_hours(self, interval_seconds=5):
+        """Box-wide pod-hours per policy; INTERVAL as in scale.py:84."""
+        return [int(s[0]) * interval_seconds / 3600.0 for s in self.sums]
+
+    def patch_bodies(self, resource_type='deployment', resource=0, policy=0):
+        """The bodies scale_resource would have sent (autoscaler.py:232,236),
+        reconstructed from the dense trajectory of one resource."""
+        field = RESOURCE_FIELD[resource_type]
+        out = []
+        prev = int(self._cur0[resource])
+        for t, v in enumerate(self.dense[policy, :, resource]):
+            v = int(v)
+            if v != prev:
+                out.append((t, {'spec': {field: v}}))
+            prev = v
+        return out
+
+
+def _check_type(resource_type, managed=('deployment', 'job')):
+    if resource_type not in managed:
+        raise ValueError('`resource_type` must be one of {}. Got {}.'.format(set(managed), resource_type))
+
+
+def _to_device_i32(x, torch, what):
+    if x is None:
+        return None
+    if isinstance(x, torch.Tensor):
+        if x.dtype != torch.int32:
+            raise TypeError('%s must be int32' % what)
+        return x.contiguous().to('cuda')
+    a = np.asarray(x)
+    if a.size and (a.min() < -(2 ** 31) or a.max() >= 2 ** 31):
+        raise OverflowError('%s must fit in int32' % what)
+    return torch.from_numpy(np.ascontiguousarray(a, dtype=np.int32)).to('cuda')
+
+
+def replay_fleet(llen, policies, inprog=None, group_off=None, cur0=None, want_totals=True,
+                 want_dense=False, resource_type='deployment'):
+    """Replay many resources at once.
+
+    llen       int32 [T][Q] (numpy or CUDA tensor), tick-major
+    inprog     None | [Q] | [T][Q]
+    group_off  None (every queue is its own resource) | uint64 [R+1]
+    cur0       None | int32 [R]
+    policies   sequence of (keys_per_pod, min_pods, max_pods)
+    """
+    _check_type(resource_type)
+    torch = engine.require_cuda()
+    d_llen = _to_device_i32(llen, torch, 'llen')
+    T, Q = int(d_llen.shape[0]), int(d_llen.shape[1])
+    d_ip = _to_device_i32(inprog, torch, 'inprog')
+    mode = 0 if d_ip is None else (1 if d_ip.dim() == 1 else 2)
+    d_go = None
+    R = Q
+    if group_off is not None:
+        go = np.ascontiguousarray(group_off, dtype=np.uint64)
+        if go[0] != 0 or go[-1] != Q or (np.diff(go.astype(np.int64)) < 0).any():
+            raise ValueError('group_off must rise from 0 to Q')
+        R = len(go) - 1
+        d_go = torch.from_numpy(go.view(np.int64)).to('cuda')
+    d_c0 = _to_device_i32(cur0, torch, 'cur0')
+    out = engine.replay(d_llen, T, Q, policies, d_inprog=d_ip, inprog_mode=mode, d_group_off=d_go,
+                        n_resources=R, d_cur0=d_c0, want_totals=want_totals, want_sums=True,
+                        want_dense=want_dense)
+    res = ReplayResult(policies,
+                       totals=engine.totals_to_host(out['totals']) if want_totals else None,
+                       sums=out['sums'].cpu().numpy(),
+                       dense=out['dense'].cpu().numpy() if want_dense else None, n_ticks=T)
+    res._cur0 = np.zeros(R, dtype=np.int64) if cur0 is None else np.asarray(cur0, dtype=np.int64)
+    return res
+
+
+def replay_one(queue_names, llen_trace, policies, inprog=None, current_pods=0,
+               resource_type='deployment', managed=('deployment', 'job'), want_dense=False):
+    """One resource fed by ``len(queue_names)`` queues (what one reference pod
+    manages): llen_trace [T][Q] in the order of ``queue_names``."""
+    _check_type(resource_type, managed)
+    a = np.asarray(llen_trace)
+    if a.ndim != 2 or a.shape[1] != len(queue_names):
+        raise ValueError('llen_trace must be [T][%d]' % len(queue_names))
+    return replay_fleet(a, policies, inprog=inprog,
+                        group_off=np.array([0, len(queue_names)], dtype=np.uint64),
+                        cur0=np.array([current_pods], dtype=np.int64), want_dense=want_dense,
+                        resource_type=resource_type)
+
+
+# --------------------------------------------------------------------------
+# sharding over the GPUs of one box
+# --------------------------------------------------------------------------
+def shard_range(n_units, rank, world_size, align=1):
+    """Contiguous share [lo, hi) of ``n_units`` for ``rank``; boundaries are
+    multiples of ``align`` (4 keeps the vectorised replay path)."""
+    if world_size < 1 or not 0 <= rank < world_size:
+        raise ValueError('bad rank/world_size')
+    blocks = (n_units + align - 1) // align
+    lo = (blocks * rank) // world_size * align
+    hi = (blocks * (rank + 1)) // world_size * align
+    return min(lo, n_units), min(hi, n_units)
+
+
+def shard_groups(group_off, rank, world_size):
+    """Share of RESOURCES for ``rank`` (all queues of a resource stay together):
+    returns (r_lo, r_hi, q_lo, q_hi, local_group_off)."""
+    go = np.asarray(group_off, dtype=np.uint64)
+    r_lo, r_hi = shard_range(len(go) - 1, rank, world_size)
+    q_lo, q_hi = int(go[r_lo]), int(go[r_hi])
+    return r_lo, r_hi, q_lo, q_hi, (go[r_lo:r_hi + 1] - go[r_lo]).astype(np.uint64)
+
+
+def allreduce_sum_(t, group=None):
+    """Box-wide integer totals: one all-reduce (NCCL over NVLink for CUDA tensors,
+    gloo in the CPU tests).  Integer sums are order independent, so the result is
+    bit-exact at every world size.  No-op without an initialised process group."""
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    return t

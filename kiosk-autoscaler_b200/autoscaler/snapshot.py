@@ -1,0 +1,129 @@
+"""Key-snapshot ingest and the snapshot-backed Redis seam.
+
+The reference walks the whole keyspace over TCP once per queue
+(autoscaler.py:69-71 of the reference).  Here the keyspace is taken ONCE,
+reduced to fixed-width heads (the first ``rec_bytes`` bytes of every key, zero
+padded) and handed to the match kernel, which counts every queue in one pass.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from autoscaler import engine
+
+
+class KeySnapshot(object):
+    """A keyspace snapshot as a blob of key bytes + offsets (host side).
+
+    Heads are packed on demand for a given record width; a snapshot built
+    straight from packed heads (``from_heads``) has no blob.
+    """
+
+    def __init__(self, blob=None, off=None, sep_bytes=0, heads=None):
+        self.blob = blob
+        self.off = off
+        self.sep_bytes = sep_bytes
+        self._heads = {} if heads is None else {heads.shape[1]: heads}
+        self._device = {}
+
+    # -- constructors -------------------------------------------------------
+    @classmethod
+    def from_keys(cls, keys):
+        """From an iterable of keys (bytes or str; str is encoded as UTF-8 the
+        way the reference's client decodes them, redis.py:159-161)."""
+        enc = [k if isinstance(k, (bytes, bytearray)) else str(k).encode('utf-8') for k in keys]
+        off = np.zeros(len(enc) + 1, dtype=np.uint64)
+        if enc:
+            off[1:] = np.cumsum([len(k) for k in enc], dtype=np.uint64)
+        blob = np.frombuffer(b''.join(enc) + b'\0', dtype=np.uint8)
+        return cls(blob=blob, off=off)
+
+    @classmethod
+    def from_blob(cls, blob, off):
+        return cls(blob=np.ascontiguousarray(blob, dtype=np.uint8),
+                   off=np.ascontiguousarray(off, dtype=np.uint64))
+
+    @classmethod
+    def from_dump(cls, data):
+        """From a newline-separated key dump (``redis-cli --scan`` output)."""
+        blob = np.frombuffer(bytes(data), dtype=np.uint8)
+        return cls(blob=blob, off=engine.index_lines_host(blob), sep_bytes=1)
+
+    @classmethod
+    def from_heads(cls, heads):
+        """From already packed heads: uint8 [n][rec_bytes] numpy array or tensor."""
+        return cls(heads=heads)
+
+    @classmethod
+    def from_redis(cls, redis_client, match='processing-*', count=1000):
+        """One SCAN of a live server through any client exposing ``scan_iter``
+        (the RedisClient seam, redis.py:163-202 of the reference).  Only keys
+        that can match some ``processing-<q>:*`` are fetched."""
+        return cls.from_keys(list(redis_client.scan_iter(match=match, count=count)))
+
+    # -- access -------------------------------------------------------------
+    def __len__(self):
+        if self.off is not None:
+            return len(self.off) - 1
+        return next(iter(self._heads.values())).shape[0]
+
+    def heads(self, rec_bytes):
+        """uint8 [n][rec_bytes] host heads for this width."""
+        if rec_bytes not in self._heads:
+            if self.off is None:
+                have = next(iter(self._heads))
+                raise ValueError('snapshot was built from %d-byte heads; %d-byte heads needed '
+                                 '(a queue name is too long for it)' % (have, rec_bytes))
+            self._heads[rec_bytes] = engine.pack_heads_host(self.blob, self.off, rec_bytes,
+                                                            sep_bytes=self.sep_bytes)
+        return self._heads[rec_bytes]
+
+    def device_heads(self, rec_bytes, device='cuda'):
+        """Heads resident in HBM (cached per width)."""
+        torch = engine.require_cuda()
+        key = (rec_bytes, str(device))
+        if key not in self._device:
+            h = self.heads(rec_bytes)
+            if isinstance(h, np.ndarray):
+                h = torch.from_numpy(h)
+            self._device[key] = h.to(device, non_blocking=True) if h.device.type == 'cpu' else h
+        return self._device[key]
+
+
+def tally_snapshot(snapshot, queue_names, device='cuda'):
+    """SCAN-count term for every queue over one snapshot: list of int, in the
+    order of ``queue_names`` (autoscaler.py:69-71 of the reference)."""
+    names = list(queue_names)
+    for q in names:
+        if any(ch in engine.GLOB_META for ch in engine.encode_name(q)):
+            engine.check(engine.KAS_ERR_GLOB_META, 'tally of queue %r' % (q,))
+    torch = engine.require_cuda()
+    rec_bytes = engine.rec_bytes_for(names)
+    if rec_bytes > engine.MAX_REC_BYTES:
+        raise engine.KasError(engine.KAS_ERR_UNSUPPORTED, 'tally',
+                              'queue names longer than %d bytes' % (engine.MAX_REC_BYTES - 12))
+    table = torch.from_numpy(engine.build_prefix_table(names, rec_bytes)).to(device)
+    heads = snapshot.device_heads(rec_bytes, device)
+    counts = engine.match_count(heads, len(snapshot), rec_bytes, table, len(names))
+    return [int(c) for c in engine.counts_to_host(counts)]
+
+
+class SnapshotRedis(object):
+    """A Redis stand-in over a key snapshot: what the offline replay feeds the
+    unchanged ``Autoscaler``.  ``llen`` answers from ``lists``;
+    ``key_snapshot()`` hands the snapshot to ``Autoscaler.tally_queues``."""
+
+    def __init__(self, snapshot=None, lists=None):
+        self.snapshot = snapshot if snapshot is not None else KeySnapshot.from_keys([])
+        self.lists = dict(lists or {})
+
+    def llen(self, name):
+        return int(self.lists.get(name, 0))
+
+    def key_snapshot(self):
+        return self.snapshot
+
+    def scan_iter(self, match=None, count=None):
+        raise NotImplementedError(
+            'SnapshotRedis does not iterate keys on the host; the tally runs on the GPU '
+            '(Autoscaler.tally_queues uses key_snapshot())')

@@ -1,0 +1,60 @@
+// kas_common.cuh -- shared helpers for libkas (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/kas.h"
+
+namespace kas {
+
+void set_cuda_error(cudaError_t e, const char *where);
+
+#define KAS_CUDA_TRY(expr)                                    \
+    do {                                                      \
+        cudaError_t _e = (expr);                              \
+        if (_e != cudaSuccess) {                              \
+            ::kas::set_cuda_error(_e, #expr);                 \
+            return KAS_ERR_CUDA;                              \
+        }                                                     \
+    } while (0)
+
+// SM count of the current device (cached per device by the caller's thread).
+int sm_count();
+
+static inline bool aligned(const void *p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
+
+#ifdef __CUDACC__
+// Streaming 128-bit load: read-once data, keep it out of L1.
+__device__ __forceinline__ uint4 ldg_stream_128(const void *p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+// 128-bit load that may allocate in L1 (used when the neighbouring 16 bytes of
+// the same sector are fetched by the next instruction of the same thread).
+__device__ __forceinline__ uint4 ldg_nc_128(const void *p) {
+    uint4 r;
+    asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+// sm_100 256-bit load (LDG.E.256): one whole 32-byte sector per thread.
+__device__ __forceinline__ void ldg_stream_256(const void *p, uint32_t (&r)[8]) {
+    asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]),
+                   "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "l"(p));
+}
+__device__ __forceinline__ int4 ldg_stream_i4(const void *p) {
+    int4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ int ldg_stream_i32(const void *p) {
+    int r;
+    asm volatile("ld.global.nc.L1::no_allocate.s32 %0, [%1];" : "=r"(r) : "l"(p));
+    return r;
+}
+#endif
+
+}  // namespace kas

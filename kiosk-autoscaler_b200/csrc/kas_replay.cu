@@ -1,0 +1,476 @@
+// kas_replay.cu -- K2: fused tally + desired-pods + clamp + hysteresis replay
+// over a queue-depth trace, the element-wise decision kernel behind the scalar
+// API, and the synthetic trace generator.
+//
+// Takes over T iterations of Autoscaler.scale (autoscaler.py:244-260) for R
+// resources and S policies.  Pure integer work, HBM-bound at S = 1 (4 bytes of
+// trace per decision) and ALU-bound under a policy sweep; nothing here is a
+// contraction, so no tensor cores.  Ticks of one resource are sequentially
+// dependent (cur[t+1] = desired[t]); resources and policies are independent,
+// so a thread owns VEC adjacent resources x SP policies and marches down the
+// tick-major trace, whose rows a warp reads as one contiguous 128/512-byte run.
+#include "kas_common.cuh"
+
+#include <limits.h>
+
+namespace kas {
+
+constexpr int kReplayThreads = 128;
+constexpr int kMaxPoliciesPerLaunch = 32;
+constexpr int kTickUnroll = 8;
+
+struct PolDev {
+    uint64_t magic;  // ceil(2^64 / |kpp|); 0 when |kpp| == 1
+    int32_t mn, mx;
+    int32_t neg;     // -1 when kpp < 0, else 0
+    int32_t pad;
+};
+
+struct ReplayParams {
+    const int32_t *llen;
+    const int32_t *inprog;
+    const uint64_t *group_off;
+    const int32_t *cur0;
+    kas_totals *totals;
+    unsigned long long *sums;
+    int32_t *dense;
+    uint64_t Q, R;
+    uint32_t T;
+    uint32_t S;            // total policies (row stride of totals)
+    uint32_t pol_first;    // global index of pol[0]
+    uint32_t pol_count;    // policies in this launch
+    int32_t inprog_mode;
+    PolDev pol[kMaxPoliciesPerLaunch];
+};
+
+// clip_pod_count (autoscaler.py:197-213), 32-bit form.  if/elif order kept.
+__device__ __forceinline__ int32_t clip32(int32_t d, int32_t mn, int32_t mx, int32_t cur) {
+    d = d > mx ? mx : (d < mn ? mn : d);
+    return (d > 0 && d < cur) ? cur : d;
+}
+// Same with a 64-bit candidate (a sum of per-queue decisions, or a quotient).
+__device__ __forceinline__ int32_t clip64(int64_t d, int32_t mn, int32_t mx, int32_t cur) {
+    int32_t r = d > (int64_t)mx ? mx : (d < (int64_t)mn ? mn : (int32_t)d);
+    return (r > 0 && r < cur) ? cur : r;
+}
+
+// tally // kpp with Python floor semantics for |tally| <= 2^32, any kpp != 0.
+__device__ __forceinline__ int64_t floordiv_any(int64_t tally, const PolDev &p) {
+    const int64_t t2 = (tally ^ (int64_t)p.neg) - (int64_t)p.neg;  // negate when kpp < 0
+    const int64_t s = t2 >> 63;
+    const uint64_t u = (uint64_t)(t2 ^ s);                          // floor(t/d) = ~((~t)/d), t < 0
+    const uint64_t q = p.magic ? __umul64hi(p.magic, u) : u;
+    return (int64_t)q ^ s;
+}
+
+// get_desired_pods (autoscaler.py:215-219) for one queue.
+template <bool GENERIC>
+__device__ __forceinline__ int32_t decide(int32_t llen, int32_t inprog, const PolDev &p, int32_t cur) {
+    if (!GENERIC && ((llen | inprog) >= 0)) {
+        // kpp >= 1 and a non-negative tally < 2^32: 32-bit quotient by multiply-high
+        const uint32_t u = (uint32_t)llen + (uint32_t)inprog;
+        const uint32_t q = p.magic ? (uint32_t)__umul64hi(p.magic, (uint64_t)u) : u;
+        const int32_t d = (int32_t)min(q, 0x7FFFFFFFu);  // saturating keeps every comparison's outcome
+        return clip32(d, p.mn, p.mx, cur);
+    }
+    return clip64(floordiv_any((int64_t)llen + (int64_t)inprog, p), p.mn, p.mx, cur);
+}
+
+__device__ __forceinline__ long long warp_sum_ll(long long v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+    return v;
+}
+
+// ---- every queue is its own resource (R == Q) ------------------------------
+template <int VEC, int SP, bool TICKIP, bool GENERIC>
+__global__ void __launch_bounds__(kReplayThreads)
+replay_identity_kernel(const __grid_constant__ ReplayParams P) {
+    constexpr int U = kTickUnroll;
+    const uint64_t r0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
+    const bool valid = r0 < P.R;
+    const uint32_t pbase = blockIdx.y * SP;   // index into P.pol
+    const uint32_t T = P.T;
+    const uint64_t Q = P.Q;
+
+    int32_t cur[SP][VEC];
+    long long pt[SP][VEC];
+    uint32_t np[SP][VEC];
+    int32_t ipq[VEC];
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) {
+        const int32_t c0 = (valid && P.cur0) ? P.cur0[r0 + v] : 0;
+        ipq[v] = (valid && P.inprog_mode == 1) ? P.inprog[r0 + v] : 0;
+#pragma unroll
+        for (int s = 0; s < SP; ++s) { cur[s][v] = c0; pt[s][v] = 0; np[s][v] = 0u; }
+    }
+
+    if (valid) {
+        const int32_t *lrow = P.llen + r0;
+        const int32_t *irow = TICKIP ? P.inprog + r0 : nullptr;
+        auto step = [&](uint32_t t, const int32_t (&l)[VEC], const int32_t (&ip)[VEC]) {
+#pragma unroll
+            for (int s = 0; s < SP; ++s) {
+                if (pbase + s < P.pol_count) {
+                    const PolDev &p = P.pol[pbase + s];
+#pragma unroll
+                    for (int v = 0; v < VEC; ++v) {
+                        const int32_t c = cur[s][v];
+                        const int32_t d = decide<GENERIC>(l[v], ip[v], p, c);     // :255-257
+                        const int32_t want = clip32(d, p.mn, p.mx, c);            // :259
+                        np[s][v] += (want != c);                                  // :227
+                        cur[s][v] = want;
+                        pt[s][v] += want;
+                    }
+                    if (P.dense) {
+                        int32_t *o = P.dense + ((uint64_t)(P.pol_first + pbase + s) * T + t) * P.R + r0;
+                        if constexpr (VEC == 4)
+                            *reinterpret_cast<int4 *>(o) = make_int4(cur[s][0], cur[s][1], cur[s][2], cur[s][3]);
+                        else
+                            o[0] = cur[s][0];
+                    }
+                }
+            }
+        };
+        uint32_t t0 = 0;
+        for (; t0 + U <= T; t0 += U) {
+            int32_t l[U][VEC], ip[U][VEC];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const uint64_t o = (uint64_t)(t0 + u) * Q;
+                if constexpr (VEC == 4) {
+                    const int4 a = ldg_stream_i4(lrow + o);
+                    l[u][0] = a.x; l[u][1] = a.y; l[u][2] = a.z; l[u][3] = a.w;
+                    if constexpr (TICKIP) {
+                        const int4 b = ldg_stream_i4(irow + o);
+                        ip[u][0] = b.x; ip[u][1] = b.y; ip[u][2] = b.z; ip[u][3] = b.w;
+                    }
+                } else {
+                    l[u][0] = ldg_stream_i32(lrow + o);
+                    if constexpr (TICKIP) ip[u][0] = ldg_stream_i32(irow + o);
+                }
+                if constexpr (!TICKIP) {
+#pragma unroll
+                    for (int v = 0; v < VEC; ++v) ip[u][v] = ipq[v];
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) step(t0 + u, l[u], ip[u]);
+        }
+        for (; t0 < T; ++t0) {
+            int32_t l[VEC], ip[VEC];
+            const uint64_t o = (uint64_t)t0 * Q;
+#pragma unroll
+            for (int v = 0; v < VEC; ++v) {
+                l[v] = ldg_stream_i32(lrow + o + v);
+                ip[v] = TICKIP ? ldg_stream_i32(irow + o + v) : ipq[v];
+            }
+            step(t0, l, ip);
+        }
+        if (P.totals) {
+#pragma unroll
+            for (int s = 0; s < SP; ++s)
+                if (pbase + s < P.pol_count)
+#pragma unroll
+                    for (int v = 0; v < VEC; ++v) {
+                        kas_totals o;
+                        o.pod_ticks = pt[s][v];
+                        o.n_patches = np[s][v];
+                        o.final_current = cur[s][v];
+                        P.totals[(r0 + v) * P.S + P.pol_first + pbase + s] = o;
+                    }
+        }
+    }
+    if (P.sums) {
+#pragma unroll
+        for (int s = 0; s < SP; ++s) {
+            if (pbase + s < P.pol_count) {   // uniform across the block
+                long long a = 0, b = 0, c = 0;
+                if (valid) {
+#pragma unroll
+                    for (int v = 0; v < VEC; ++v) { a += pt[s][v]; b += np[s][v]; c += cur[s][v]; }
+                }
+                a = warp_sum_ll(a); b = warp_sum_ll(b); c = warp_sum_ll(c);
+                if ((threadIdx.x & 31) == 0) {
+                    unsigned long long *o = P.sums + 3ull * (P.pol_first + pbase + s);
+                    atomicAdd(o + 0, (unsigned long long)a);
+                    atomicAdd(o + 1, (unsigned long long)b);
+                    atomicAdd(o + 2, (unsigned long long)c);
+                }
+            }
+        }
+    }
+}
+
+// ---- resources that own several queues (CSR groups) ------------------------
+template <int SP, bool GENERIC>
+__global__ void __launch_bounds__(kReplayThreads)
+replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
+    const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = r < P.R;
+    const uint32_t pbase = blockIdx.y * SP;
+    const uint32_t T = P.T;
+    const uint64_t Q = P.Q;
+    int32_t cur[SP];
+    long long pt[SP];
+    uint32_t np[SP];
+    const int32_t c0 = (valid && P.cur0) ? P.cur0[r] : 0;
+#pragma unroll
+    for (int s = 0; s < SP; ++s) { cur[s] = c0; pt[s] = 0; np[s] = 0u; }
+    if (valid) {
+        const uint64_t q0 = P.group_off ? P.group_off[r] : r;
+        const uint64_t q1 = P.group_off ? P.group_off[r + 1] : r + 1;
+        for (uint32_t t = 0; t < T; ++t) {
+            const int32_t *lrow = P.llen + (uint64_t)t * Q;
+            const int32_t *irow = P.inprog_mode == 2 ? P.inprog + (uint64_t)t * Q : P.inprog;
+            long long sum[SP];
+#pragma unroll
+            for (int s = 0; s < SP; ++s) sum[s] = 0;
+            for (uint64_t q = q0; q < q1; ++q) {
+                const int32_t l = ldg_stream_i32(lrow + q);
+                const int32_t ip = P.inprog_mode ? __ldg(irow + q) : 0;
+#pragma unroll
+                for (int s = 0; s < SP; ++s)
+                    if (pbase + s < P.pol_count)
+                        sum[s] += decide<GENERIC>(l, ip, P.pol[pbase + s], cur[s]);   // :255-257
+            }
+#pragma unroll
+            for (int s = 0; s < SP; ++s) {
+                if (pbase + s < P.pol_count) {
+                    const PolDev &p = P.pol[pbase + s];
+                    const int32_t want = clip64(sum[s], p.mn, p.mx, cur[s]);          // :259
+                    np[s] += (want != cur[s]);
+                    cur[s] = want;
+                    pt[s] += want;
+                    if (P.dense) P.dense[((uint64_t)(P.pol_first + pbase + s) * T + t) * P.R + r] = want;
+                }
+            }
+        }
+        if (P.totals) {
+#pragma unroll
+            for (int s = 0; s < SP; ++s)
+                if (pbase + s < P.pol_count) {
+                    kas_totals o;
+                    o.pod_ticks = pt[s];
+                    o.n_patches = np[s];
+                    o.final_current = cur[s];
+                    P.totals[r * P.S + P.pol_first + pbase + s] = o;
+                }
+        }
+    }
+    if (P.sums) {
+#pragma unroll
+        for (int s = 0; s < SP; ++s) {
+            if (pbase + s < P.pol_count) {
+                long long a = valid ? pt[s] : 0, b = valid ? (long long)np[s] : 0, c = valid ? (long long)cur[s] : 0;
+                a = warp_sum_ll(a); b = warp_sum_ll(b); c = warp_sum_ll(c);
+                if ((threadIdx.x & 31) == 0) {
+                    unsigned long long *o = P.sums + 3ull * (P.pol_first + pbase + s);
+                    atomicAdd(o + 0, (unsigned long long)a);
+                    atomicAdd(o + 1, (unsigned long long)b);
+                    atomicAdd(o + 2, (unsigned long long)c);
+                }
+            }
+        }
+    }
+}
+
+// ---- element-wise decision (scalar API) ------------------------------------
+__device__ __forceinline__ long long clip_ll(long long d, long long mn, long long mx, long long cur) {
+    d = d > mx ? mx : (d < mn ? mn : d);
+    return (d > 0 && d < cur) ? cur : d;
+}
+
+__global__ void __launch_bounds__(256)
+decide_kernel(const long long *__restrict__ a, const long long *__restrict__ kpp,
+              const long long *__restrict__ mn, const long long *__restrict__ mx,
+              const long long *__restrict__ cur, uint64_t n, int mode,
+              long long *__restrict__ out, int *__restrict__ status) {
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (uint64_t)gridDim.x * blockDim.x) {
+        long long d = a[i];
+        if (mode == 0) {
+            const long long k = kpp[i];
+            if (k == 0) {            // reference: ZeroDivisionError (autoscaler.py:217)
+                *status = 1;
+                out[i] = 0;
+                continue;
+            }
+            if (d == LLONG_MIN && k == -1) {
+                d = LLONG_MAX;       // true quotient 2^63 exceeds every max_pods: the clamp picks max
+            } else {
+                long long q = d / k;
+                if ((d % k != 0) && ((d < 0) != (k < 0))) q -= 1;   // Python //
+                d = q;
+            }
+        }
+        out[i] = clip_ll(d, mn[i], mx[i], cur[i]);
+    }
+}
+
+// ---- synthetic trace (spec in DESIGN.md; twin in oracle/kas_oracle.c) ------
+__device__ __forceinline__ uint64_t mix64(uint64_t z) {
+    z += 0x9E3779B97F4A7C15ULL;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
+}
+
+__global__ void __launch_bounds__(256)
+synth_trace_kernel(uint64_t seed, uint32_t T, uint64_t q_first, uint64_t n_q, int32_t *__restrict__ out) {
+    const uint64_t total = (uint64_t)T * n_q;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t t = (uint32_t)(i / n_q);
+        const uint64_t q = q_first + (i % n_q);
+        const uint64_t epoch = t >> 6;
+        const uint64_t he = mix64(mix64(seed ^ (q * 0xD1342543DE82EF95ULL)) + epoch);
+        const uint64_t ht = mix64(he ^ ((uint64_t)t * 0x2545F4914F6CDD1DULL));
+        const uint32_t active = (uint32_t)(he % 100u) < 45u;
+        const uint32_t level = (uint32_t)((he >> 8) % 400u);
+        const uint32_t jitter = (uint32_t)(ht & 0xFFu);
+        int32_t v = 0;
+        if (active) v = (int32_t)((level * jitter) >> 7);
+        else if (jitter < 10u) v = (int32_t)((ht >> 8) & 3u);
+        out[i] = v;
+    }
+}
+
+template <int VEC, int SP, bool TICKIP>
+static void launch_identity(const ReplayParams &P, bool generic, cudaStream_t stream) {
+    const uint64_t threads = (P.R + VEC - 1) / VEC;
+    dim3 grid((unsigned)((threads + kReplayThreads - 1) / kReplayThreads), (P.pol_count + SP - 1) / SP);
+    if (generic) replay_identity_kernel<VEC, SP, TICKIP, true><<<grid, kReplayThreads, 0, stream>>>(P);
+    else replay_identity_kernel<VEC, SP, TICKIP, false><<<grid, kReplayThreads, 0, stream>>>(P);
+}
+
+template <int SP>
+static void launch_grouped(const ReplayParams &P, bool generic, cudaStream_t stream) {
+    dim3 grid((unsigned)((P.R + kReplayThreads - 1) / kReplayThreads), (P.pol_count + SP - 1) / SP);
+    if (generic) replay_grouped_kernel<SP, true><<<grid, kReplayThreads, 0, stream>>>(P);
+    else replay_grouped_kernel<SP, false><<<grid, kReplayThreads, 0, stream>>>(P);
+}
+
+}  // namespace kas
+
+using namespace kas;
+
+extern "C" {
+
+int kas_replay(const kas_replay_args *a, void *stream_v) {
+    if (!a || !a->policies || a->n_policies == 0) return KAS_ERR_INVALID;
+    if (a->n_queues == 0 || a->n_resources == 0) return KAS_ERR_INVALID;
+    if (a->n_ticks && !a->d_llen) return KAS_ERR_INVALID;
+    if (a->inprog_mode < 0 || a->inprog_mode > 2) return KAS_ERR_INVALID;
+    if (a->inprog_mode != 0 && !a->d_inprog) return KAS_ERR_INVALID;
+    if (!a->d_group_off && a->n_resources != a->n_queues) return KAS_ERR_INVALID;
+    if (!a->d_totals && !a->d_sums && !a->d_dense) return KAS_ERR_INVALID;
+    if (a->n_resources > 0x7FFFFFFFull * kReplayThreads) return KAS_ERR_UNSUPPORTED;
+    if (!aligned(a->d_llen, 4) || !aligned(a->d_inprog, 4) || !aligned(a->d_dense, 4) ||
+        !aligned(a->d_totals, 8) || !aligned(a->d_sums, 8) || !aligned(a->d_group_off, 8) ||
+        !aligned(a->d_cur0, 4))
+        return KAS_ERR_ALIGNMENT;
+    bool generic = false;
+    for (uint32_t s = 0; s < a->n_policies; ++s) {
+        if (a->policies[s].keys_per_pod == 0) return KAS_ERR_ZERO_DIVISION;
+        if (a->policies[s].keys_per_pod < 0) generic = true;
+    }
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    if (a->d_sums)
+        KAS_CUDA_TRY(cudaMemsetAsync(a->d_sums, 0, sizeof(int64_t) * 3 * a->n_policies, stream));
+
+    const bool identity = a->d_group_off == nullptr;
+    const bool tickip = a->inprog_mode == 2;
+    const bool vec4 = identity && (a->n_queues % 4 == 0) && aligned(a->d_llen, 16) &&
+                      (!tickip || aligned(a->d_inprog, 16)) &&
+                      (a->inprog_mode != 1 || aligned(a->d_inprog, 4)) &&
+                      (!a->d_dense || aligned(a->d_dense, 16)) && a->n_resources >= 4096;
+
+    for (uint32_t first = 0; first < a->n_policies; first += kMaxPoliciesPerLaunch) {
+        ReplayParams P;
+        P.llen = a->d_llen;
+        P.inprog = a->d_inprog;
+        P.group_off = a->d_group_off;
+        P.cur0 = a->d_cur0;
+        P.totals = a->d_totals;
+        P.sums = reinterpret_cast<unsigned long long *>(a->d_sums);
+        P.dense = a->d_dense;
+        P.Q = a->n_queues;
+        P.R = a->n_resources;
+        P.T = a->n_ticks;
+        P.S = a->n_policies;
+        P.pol_first = first;
+        P.pol_count = a->n_policies - first < (uint32_t)kMaxPoliciesPerLaunch
+                          ? a->n_policies - first : (uint32_t)kMaxPoliciesPerLaunch;
+        P.inprog_mode = a->inprog_mode;
+        for (uint32_t s = 0; s < (uint32_t)kMaxPoliciesPerLaunch; ++s) {
+            PolDev d = {0, 0, 0, 0, 0};
+            if (s < P.pol_count) {
+                const kas_policy &p = a->policies[first + s];
+                const uint64_t ak = p.keys_per_pod < 0 ? (uint64_t)(-(int64_t)p.keys_per_pod)
+                                                       : (uint64_t)p.keys_per_pod;
+                d.magic = ak == 1 ? 0ull : (~0ull / ak) + 1ull;   // ceil(2^64/ak) (exact when ak | 2^64 too)
+                d.mn = p.min_pods;
+                d.mx = p.max_pods;
+                d.neg = p.keys_per_pod < 0 ? -1 : 0;
+            }
+            P.pol[s] = d;
+        }
+        if (identity) {
+            if (P.pol_count == 1) {
+                if (vec4) tickip ? launch_identity<4, 1, true>(P, generic, stream)
+                                 : launch_identity<4, 1, false>(P, generic, stream);
+                else tickip ? launch_identity<1, 1, true>(P, generic, stream)
+                            : launch_identity<1, 1, false>(P, generic, stream);
+            } else {
+                if (vec4) tickip ? launch_identity<4, 4, true>(P, generic, stream)
+                                 : launch_identity<4, 4, false>(P, generic, stream);
+                else tickip ? launch_identity<1, 4, true>(P, generic, stream)
+                            : launch_identity<1, 4, false>(P, generic, stream);
+            }
+        } else {
+            if (P.pol_count == 1) launch_grouped<1>(P, generic, stream);
+            else launch_grouped<4>(P, generic, stream);
+        }
+        KAS_CUDA_TRY(cudaGetLastError());
+    }
+    return KAS_OK;
+}
+
+int kas_decide(const int64_t *d_a, const int64_t *d_kpp, const int64_t *d_mn, const int64_t *d_mx,
+               const int64_t *d_cur, uint64_t n, int mode, int64_t *d_out, int32_t *d_status,
+               void *stream_v) {
+    if (mode != 0 && mode != 1) return KAS_ERR_INVALID;
+    if (n && (!d_a || !d_mn || !d_mx || !d_cur || !d_out || !d_status)) return KAS_ERR_INVALID;
+    if (n && mode == 0 && !d_kpp) return KAS_ERR_INVALID;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    if (d_status) KAS_CUDA_TRY(cudaMemsetAsync(d_status, 0, sizeof(int32_t), stream));
+    if (n == 0) return KAS_OK;
+    const int sms = sm_count();
+    if (sms <= 0) return KAS_ERR_CUDA;
+    uint64_t grid = (n + 255) / 256;
+    if (grid > (uint64_t)sms * 8) grid = (uint64_t)sms * 8;
+    decide_kernel<<<(unsigned)grid, 256, 0, stream>>>(
+        reinterpret_cast<const long long *>(d_a), reinterpret_cast<const long long *>(d_kpp),
+        reinterpret_cast<const long long *>(d_mn), reinterpret_cast<const long long *>(d_mx),
+        reinterpret_cast<const long long *>(d_cur), n, mode, reinterpret_cast<long long *>(d_out), d_status);
+    KAS_CUDA_TRY(cudaGetLastError());
+    return KAS_OK;
+}
+
+int kas_synth_trace(uint64_t seed, uint32_t n_ticks, uint64_t q_first, uint64_t n_q, int32_t *d_out,
+                    void *stream_v) {
+    if (!d_out && n_ticks && n_q) return KAS_ERR_INVALID;
+    if (n_ticks == 0 || n_q == 0) return KAS_OK;
+    const int sms = sm_count();
+    if (sms <= 0) return KAS_ERR_CUDA;
+    const uint64_t total = (uint64_t)n_ticks * n_q;
+    uint64_t grid = (total + 255) / 256;
+    if (grid > (uint64_t)sms * 16) grid = (uint64_t)sms * 16;
+    synth_trace_kernel<<<(unsigned)grid, 256, 0, static_cast<cudaStream_t>(stream_v)>>>(seed, n_ticks, q_first,
+                                                                                       n_q, d_out);
+    KAS_CUDA_TRY(cudaGetLastError());
+    return KAS_OK;
+}
+
+}  // extern "C"

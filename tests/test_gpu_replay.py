@@ -1,0 +1,127 @@
+"""K2 (replay) through the C ABI against the reference-made fixtures and the oracle."""
+import numpy as np
+import pytest
+
+from tests import helpers
+
+pytestmark = pytest.mark.gpu
+
+
+def test_golden_scale_cases():
+    import autoscaler
+    from oracle import oracle
+    for case in helpers.golden_json('scale_cases'):
+        names = list(oracle.parse_queues(case['queues'], case['delim']))
+        split = case['queues'].split(case['delim'])
+        llen = np.array([[dict(zip(split, row)).get(q, 0) for q in names] for row in case['depths']],
+                        dtype=np.int32)
+        snap = autoscaler.snapshot.KeySnapshot.from_keys(helpers.latin(case['keyspace']))
+        inprog = autoscaler.snapshot.tally_snapshot(snap, names) if len(snap) else [0] * len(names)
+        scaler = autoscaler.Autoscaler(helpers.ListRedis(), case['queues'], case['delim'])
+        res = scaler.replay(llen, [(case['kpp'], case['min'], case['max'])],
+                            inprog=np.array(inprog, dtype=np.int32), current_pods=case['cur0'],
+                            resource_type=case['type'], want_dense=True)
+        assert res.dense[0, :, 0].tolist() == case['after']
+        assert int(res.n_patches[0, 0]) == len(case['patches'])
+        field = 'replicas' if case['type'] == 'deployment' else 'parallelism'
+        assert [b['spec'][field] for _, b in res.patch_bodies(case['type'])] == case['patches']
+    with pytest.raises(ValueError):
+        scaler.replay(llen, [(1, 0, 1)], resource_type='badvalue')
+    with pytest.raises(ZeroDivisionError):
+        scaler.replay(llen, [(0, 0, 1)])
+
+
+def test_c1_reference_run():
+    """BASELINE config 1: QUEUES='predict,track', 10k keys, 10k ticks, policy sweep."""
+    import autoscaler
+    g = helpers.golden_c1()
+    snap = autoscaler.snapshot.KeySnapshot.from_keys(g['keys'])
+    scaler = autoscaler.Autoscaler(autoscaler.snapshot.SnapshotRedis(snap), 'predict,track')
+    scaler.tally_queues()
+    assert [scaler.redis_keys['predict'], scaler.redis_keys['track']] == g['snapshot_counts'].tolist()
+    res = scaler.replay(g['llen'], g['policies'], inprog=g['inprog'], want_dense=True)
+    assert res.pod_ticks[0].tolist() == g['pod_ticks'].tolist()
+    assert res.n_patches[0].tolist() == g['n_patches'].tolist()
+    assert res.final[0].tolist() == g['final'].tolist()
+    for k, si in enumerate(g['dense_idx']):
+        assert (res.dense[si, :, 0] == g['dense'][k]).all()
+    assert res.sums[:, 0].tolist() == g['pod_ticks'].tolist()
+
+
+POLICY_SETS = {
+    'one': [(1, 0, 1)],
+    'sweep': [(k, a, b) for k in (1, 2, 5, 10, 50) for a in (0, 1) for b in (1, 4, 16, 64)],
+    'quirks': [(3, 9, 5), (1, -2, 3), (2 ** 31 - 1, 0, 7), (1, 0, 2 ** 31 - 1), (7, 0, 0)],
+    'negative': [(-1, 0, 5), (-3, -4, 6), (-(2 ** 31), 0, 3), (2, 0, 4)],
+}
+
+
+@pytest.mark.parametrize('pol', list(POLICY_SETS))
+@pytest.mark.parametrize('shape', ['vec4', 'scalar', 'grouped', 'tiny'])
+@pytest.mark.parametrize('ipmode', [0, 1, 2])
+def test_random_fleets_vs_oracle(pol, shape, ipmode):
+    import autoscaler
+    from oracle import coracle
+    rng = np.random.default_rng(hash((pol, shape, ipmode)) % (2 ** 32))
+    T, Q = {'vec4': (37, 8192), 'scalar': (50, 4099), 'grouped': (41, 3000), 'tiny': (300, 3)}[shape]
+    llen, go = helpers.random_fleet(rng, T, Q, grouped=(shape == 'grouped'), neg=(pol == 'negative'))
+    if pol == 'quirks':
+        llen[rng.random(llen.shape) < 0.01] = 2 ** 31 - 1
+    inprog = None
+    if ipmode == 1:
+        inprog = rng.integers(0, 5, size=Q).astype(np.int32)
+    elif ipmode == 2:
+        inprog = rng.integers(0, 9, size=(T, Q)).astype(np.int32)
+        if pol == 'quirks':
+            inprog[rng.random(inprog.shape) < 0.01] = 2 ** 31 - 1
+    R = Q if go is None else len(go) - 1
+    cur0 = rng.integers(0, 12, size=R).astype(np.int32) if rng.random() < 0.7 else None
+    want = coracle.replay(llen, inprog, go, cur0, POLICY_SETS[pol], want_dense=True)
+    got = autoscaler.replay.replay_fleet(llen, POLICY_SETS[pol], inprog=inprog, group_off=go,
+                                         cur0=cur0, want_dense=True)
+    assert (got.dense == want['dense']).all()
+    assert (got.pod_ticks == want['pod_ticks']).all()
+    assert (got.n_patches == want['n_patches']).all()
+    assert (got.final == want['final']).all()
+    assert (got.sums[:, 0] == want['pod_ticks'].sum(0)).all()
+    assert (got.sums[:, 1] == want['n_patches'].sum(0)).all()
+    assert (got.sums[:, 2] == want['final'].astype(np.int64).sum(0)).all()
+
+
+def test_synth_trace_twin():
+    from autoscaler import engine
+    from oracle import coracle
+    d = engine.synth_trace(9, 130, 1_000_000_007, 1000)
+    assert (d.cpu().numpy() == coracle.trace_fill(9, 130, 1_000_000_007, 1000)).all()
+    assert (d == 0).float().mean().item() > 0.3
+
+
+def test_large_replay_sampled_queues():
+    """1M queues x 2000 ticks resident in HBM, generated on the device; whole
+    trajectories of sampled queues are rebuilt by the oracle's generator twin and
+    replayed on the CPU; totals are also checked against a two-shard run."""
+    import torch
+    from autoscaler import engine
+    from oracle import coracle
+    T, Q, seed = 2000, 1_000_000, 21
+    trace = engine.synth_trace(seed, T, 0, Q)
+    pol = [(1, 0, 1), (5, 0, 16), (2, 1, 64), (50, 0, 4)]
+    out = engine.replay(trace, T, Q, pol)
+    tot = engine.totals_to_host(out['totals'])
+    sums = out['sums'].cpu().numpy()
+    rng = np.random.default_rng(1)
+    for q in rng.integers(0, Q, size=24).tolist() + [0, Q - 1]:
+        col = coracle.trace_fill(seed, T, q, 1)
+        want = coracle.replay(col, None, None, None, pol)
+        assert tot['pod_ticks'][q].tolist() == want['pod_ticks'][0].tolist()
+        assert tot['n_patches'][q].tolist() == want['n_patches'][0].tolist()
+        assert tot['final_current'][q].tolist() == want['final'][0].tolist()
+    assert (sums[:, 0] == tot['pod_ticks'].sum(0)).all()
+    assert (sums[:, 1] == tot['n_patches'].astype(np.int64).sum(0)).all()
+    # sharding by resource: two halves generated independently give the same box-wide sums
+    half = Q // 2
+    acc = torch.zeros_like(out['sums'])
+    for lo in (0, half):
+        part = engine.synth_trace(seed, T, lo, half)
+        acc += engine.replay(part, T, half, pol, want_totals=False)['sums']
+    assert (acc.cpu().numpy() == sums).all()
