@@ -7,10 +7,18 @@
 // exactly once with 128/256-bit loads, the queue table lives in shared memory,
 // counts are aggregated warp -> block (shared) -> grid (one 64-bit atomic per
 // queue per block).
+//
+// Per key: test the 11-byte literal, find the ':' bytes of the name region
+// with byte-parallel arithmetic, and look the text up to the first ':' up in
+// the table (hash of the masked region words, multiply-add chain).  Only when
+// that entry says a longer queue name continues it does the walk go on to the
+// next ':' (see kas_table.h).
 #include "kas_common.cuh"
 #include "kas_table.h"
 
 #include <string.h>
+#include <map>
+#include <type_traits>
 #include <string>
 #include <vector>
 
@@ -18,38 +26,51 @@ namespace kas {
 
 constexpr int kMatchThreads = 256;
 constexpr uint32_t kNoQueue = 0xFFFFFFFFu;
+constexpr size_t kMaxMatchSmem = 200 * 1024;
 
 // ':' detector: 0x80 in every byte of w that equals 0x3A (exact, no carries).
 __device__ __forceinline__ uint32_t colon_flags(uint32_t w) {
-    uint32_t v = w ^ 0x3A3A3A3Au;
-    uint32_t t = ((v & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | v;
+    const uint32_t v = w ^ 0x3A3A3A3Au;
+    const uint32_t t = ((v & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | v;
     return ~t & 0x80808080u;
 }
-// 0x80-per-byte flags -> 4-bit mask (bit i <=> byte i).
-__device__ __forceinline__ uint32_t flags_to_nibble(uint32_t f) {
-    return (((f >> 7) * 0x00204081u) >> 21) & 0xFu;
-}
+// 0x80-per-byte flags -> the same four bits in the top nibble (no carries:
+// every partial product lands on its own bit).
+__device__ __forceinline__ uint32_t flags_to_top_nibble(uint32_t f) { return f * 0x00204081u; }
 
 template <int NCHUNK>
 struct MatchCfg {
     static constexpr int kRecWords = 4 * NCHUNK;
-    static constexpr int kRegionWords = (16 * NCHUNK - (int)kLiteralLen + 3) / 4;
+    static constexpr int kRW = (16 * NCHUNK - (int)kLiteralLen + 3) / 4;   // region words
+    static constexpr int kRWP = (kRW + 3) / 4 * 4;                         // padded to 128-bit rows
+    static constexpr int kEW = kRW + 2;                                    // entry words
+    static constexpr int kRows = 16 * NCHUNK - (int)kLiteralLen;           // name lengths 0..W-12
     static constexpr int kKeysPerThread = NCHUNK <= 2 ? 4 : 2;
+    using mask_t = typename std::conditional<(kRows <= 32), uint32_t, uint64_t>::type;   // one bit per name length
+    static_assert(kEW % 4 == 0, "entry rows must be 128-bit multiples");
 };
 
-// Examine one record held in registers.  Returns the id of the first matching
-// queue (kNoQueue if none); further matches of the same key (nested names
+struct MatchSmem {
+    const uint32_t *masks;    // [kRows][kRWP]
+    const uint32_t *entries;  // [n_slots][kEW]
+    uint32_t *hist;           // [n_prefix]
+};
+
+// Examine one record held in registers.  Returns the id of the first queue it
+// counts for (kNoQueue if none); further queues of the same key (nested names
 // such as "predict" and "predict:zstack") are added to the block histogram
 // directly, they are rare.
+template <typename M> __device__ __forceinline__ int first_bit(M m);
+template <> __device__ __forceinline__ int first_bit<uint32_t>(uint32_t m) { return __ffs((int)m) - 1; }
+template <> __device__ __forceinline__ int first_bit<uint64_t>(uint64_t m) { return __ffsll((long long)m) - 1; }
+
 template <int NCHUNK>
-__device__ __forceinline__ uint32_t match_one(const uint32_t (&x)[4 * NCHUNK],
-                                              const uint32_t *__restrict__ s_words,
-                                              const uint32_t *__restrict__ s_qid,
-                                              uint32_t *__restrict__ s_hist,
-                                              uint32_t n_slots, uint32_t log2_slots,
-                                              uint64_t len_mask) {
-    constexpr int XW = MatchCfg<NCHUNK>::kRecWords;
-    constexpr int RW = MatchCfg<NCHUNK>::kRegionWords;
+__device__ __forceinline__ uint32_t match_one(const uint32_t (&x)[4 * NCHUNK], const MatchSmem &sm,
+                                              uint32_t slot_mask, uint32_t slot_shift,
+                                              typename MatchCfg<NCHUNK>::mask_t len_mask) {
+    using Cfg = MatchCfg<NCHUNK>;
+    using mask_t = typename Cfg::mask_t;
+    constexpr int XW = Cfg::kRecWords, RW = Cfg::kRW, RWP = Cfg::kRWP, EW = Cfg::kEW;
     // "processing-" = 70 72 6f 63 | 65 73 73 69 | 6e 67 2d
     const bool literal = (x[0] == 0x636F7270u) & (x[1] == 0x69737365u) &
                          ((x[2] & 0x00FFFFFFu) == 0x002D676Eu);
@@ -59,39 +80,72 @@ __device__ __forceinline__ uint32_t match_one(const uint32_t (&x)[4 * NCHUNK],
 #pragma unroll
         for (int k = 0; k < RW; ++k)
             r[k] = (3 + k < XW) ? __byte_perm(x[2 + k], x[3 + k], 0x6543) : (x[2 + k] >> 24);
-        uint64_t cand = 0;
+        // bit L of `colons` <=> region byte L is ':'
+        mask_t colons = 0;
+        if constexpr (sizeof(mask_t) == 4) {
 #pragma unroll
-        for (int k = 0; k < RW; ++k)
-            cand |= (uint64_t)flags_to_nibble(colon_flags(r[k])) << (4 * k);
-        cand &= len_mask;
-        while (cand) {
-            const int L = __ffsll((long long)cand) - 1;
-            cand &= cand - 1;
-            const int nbytes = L + 1;
-            uint32_t m[RW];
-            uint32_t h = hash_init((uint32_t)nbytes);
+            for (int k = RW - 1; k >= 0; --k)
+                colons = __funnelshift_l(flags_to_top_nibble(colon_flags(r[k])), colons, 4);
+        } else {
+#pragma unroll
+            for (int k = RW - 1; k >= 0; --k)
+                colons = (colons << 4) | (mask_t)(flags_to_top_nibble(colon_flags(r[k])) >> 28);
+        }
+        // Only positions that are the length of some entry can match.  Dropping the
+        // others up front is safe because the table is closed under cutting at inner
+        // colons: a candidate that spans a colon at a non-entry length is no entry.
+        colons &= len_mask;
+        while (colons) {
+            const int L = first_bit<mask_t>(colons);
+            colons &= colons - 1;
+            const uint32_t nbytes = (uint32_t)L + 1u;
+            // masked region words and their hash
+            uint32_t m[RWP];
+            const uint4 *mrow = reinterpret_cast<const uint4 *>(sm.masks + (uint32_t)L * RWP);
+#pragma unroll
+            for (int j = 0; j < RWP / 4; ++j) {
+                const uint4 v = mrow[j];
+                m[4 * j] = v.x; m[4 * j + 1] = v.y; m[4 * j + 2] = v.z; m[4 * j + 3] = v.w;
+            }
+            uint32_t h = 0;
 #pragma unroll
             for (int k = 0; k < RW; ++k) {
-                m[k] = r[k] & word_mask(k, nbytes);
-                h = hash_step(h, m[k]);
+                m[k] &= r[k];
+                h += m[k] * hash_word_constant(k);
             }
-            uint32_t slot = hash_slot(h, log2_slots);
+            const uint32_t tag = hash_finish(h, nbytes);
+            uint32_t slot = hash_slot(tag, slot_shift);
+            uint32_t meta = 0;
+            bool hit = false;
             for (;;) {
-                const uint32_t w0 = s_words[slot];
-                if (w0 == 0u) break;
-                if (w0 == m[0]) {
-                    bool eq = true;
+                const uint32_t *e = sm.entries + slot * EW;
+                const uint32_t etag = e[RW];
+                if (etag == 0u) break;                     // empty slot: not an entry
+                if (etag == tag) {
+                    uint32_t w[EW];
 #pragma unroll
-                    for (int k = 1; k < RW; ++k) eq &= (s_words[k * n_slots + slot] == m[k]);
-                    if (eq) {
-                        const uint32_t q = s_qid[slot];
-                        if (first == kNoQueue) first = q;
-                        else atomicAdd(&s_hist[q], 1u);
+                    for (int j = 0; j < EW / 4; ++j) {
+                        const uint4 v = reinterpret_cast<const uint4 *>(e)[j];
+                        w[4 * j] = v.x; w[4 * j + 1] = v.y; w[4 * j + 2] = v.z; w[4 * j + 3] = v.w;
+                    }
+                    uint32_t diff = 0;
+#pragma unroll
+                    for (int k = 0; k < RW; ++k) diff |= w[k] ^ m[k];
+                    if (diff == 0u) {
+                        meta = w[RW + 1];
+                        hit = true;
                         break;
                     }
                 }
-                slot = (slot + 1) & (n_slots - 1);
+                slot = (slot + 1) & slot_mask;
             }
+            if (!hit) break;
+            const uint32_t q = meta & ~kExtFlag;
+            if (q != kVirtualQueue) {
+                if (first == kNoQueue) first = q;
+                else atomicAdd(&sm.hist[q], 1u);
+            }
+            if (!(meta & kExtFlag)) break;                 // no longer queue name continues this one
         }
     }
     return first;
@@ -102,10 +156,11 @@ __global__ void __launch_bounds__(kMatchThreads)
 match_count_kernel(const uint8_t *__restrict__ heads, uint64_t n_keys,
                    const uint32_t *__restrict__ tbl, uint32_t n_prefix, uint32_t n_slots,
                    uint32_t log2_slots, unsigned long long *__restrict__ counts) {
-    constexpr int XW = MatchCfg<NCHUNK>::kRecWords;
-    constexpr int RW = MatchCfg<NCHUNK>::kRegionWords;
-    constexpr int U = MatchCfg<NCHUNK>::kKeysPerThread;
-    extern __shared__ uint32_t smem[];
+    using Cfg = MatchCfg<NCHUNK>;
+    constexpr int XW = Cfg::kRecWords;
+    constexpr int U = Cfg::kKeysPerThread;
+    extern __shared__ uint4 smem4[];
+    uint32_t *smem = reinterpret_cast<uint32_t *>(smem4);
 
     // Sizes come from the launch (they size the shared memory); a table image that
     // disagrees with them is reported by poisoning the counts, never by reading past it.
@@ -114,16 +169,20 @@ match_count_kernel(const uint8_t *__restrict__ heads, uint64_t n_keys,
             for (uint32_t i = threadIdx.x; i < n_prefix; i += blockDim.x) counts[i] = ~0ull;
         return;
     }
-    const uint64_t len_mask = (uint64_t)tbl[4] | ((uint64_t)tbl[5] << 32);
-    uint32_t *s_words = smem;                      // [RW][n_slots]
-    uint32_t *s_qid = s_words + RW * n_slots;      // [n_slots]
-    uint32_t *s_hist = s_qid + n_slots;            // [n_prefix]
-    for (uint32_t i = threadIdx.x; i < (RW + 1) * n_slots; i += blockDim.x)
-        smem[i] = tbl[kTableHeaderWords + i];
-    for (uint32_t i = threadIdx.x; i < n_prefix; i += blockDim.x) s_hist[i] = 0u;
+    const typename Cfg::mask_t len_mask =
+        (typename Cfg::mask_t)((uint64_t)tbl[4] | ((uint64_t)tbl[5] << 32));
+    const uint32_t slot_shift = 32u - log2_slots;   // n_slots >= 8
+    const uint32_t image_words = Cfg::kRows * Cfg::kRWP + n_slots * Cfg::kEW;
+    for (uint32_t i = threadIdx.x; i < image_words; i += blockDim.x) smem[i] = tbl[kTableHeaderWords + i];
+    MatchSmem sm;
+    sm.masks = smem;
+    sm.entries = smem + Cfg::kRows * Cfg::kRWP;
+    sm.hist = smem + image_words;
+    for (uint32_t i = threadIdx.x; i < n_prefix; i += blockDim.x) sm.hist[i] = 0u;
     __syncthreads();
 
     const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t slot_mask = n_slots - 1;
     const uint64_t tile = (uint64_t)blockDim.x * U;
     for (uint64_t base = (uint64_t)blockIdx.x * tile; base < n_keys; base += (uint64_t)gridDim.x * tile) {
         uint32_t x[U][XW];
@@ -158,32 +217,37 @@ match_count_kernel(const uint8_t *__restrict__ heads, uint64_t n_keys,
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const uint32_t q = match_one<NCHUNK>(x[u], s_words, s_qid, s_hist, n_slots, log2_slots, len_mask);
+            const uint32_t q = match_one<NCHUNK>(x[u], sm, slot_mask, slot_shift, len_mask);
             __syncwarp();
             if (__any_sync(0xFFFFFFFFu, q != kNoQueue)) {
                 // warp histogram: lanes holding the same queue elect one adder
                 const uint32_t peers = __match_any_sync(0xFFFFFFFFu, q);
                 if (q != kNoQueue && lane == (uint32_t)(__ffs(peers) - 1))
-                    atomicAdd(&s_hist[q], (uint32_t)__popc(peers));
+                    atomicAdd(&sm.hist[q], (uint32_t)__popc(peers));
             }
         }
     }
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < n_prefix; i += blockDim.x) {
-        const uint32_t c = s_hist[i];
+        const uint32_t c = sm.hist[i];
         if (c) atomicAdd(&counts[i], (unsigned long long)c);
     }
 }
 
-static size_t match_smem_bytes(uint32_t n_prefix, uint32_t n_slots, uint32_t rec_bytes) {
-    return ((size_t)(region_words(rec_bytes) + 1) * n_slots + n_prefix) * sizeof(uint32_t);
-}
-
 static uint32_t slots_for(uint32_t n_prefix) {
     uint32_t want = n_prefix <= 256 ? 4 * n_prefix : 2 * n_prefix;
-    uint32_t s = 4;
+    uint32_t s = 8;
     while (s < want) s <<= 1;
     return s;
+}
+
+static size_t image_words(uint32_t n_prefix, uint32_t rec_bytes) {
+    return (size_t)length_rows(rec_bytes) * region_words_padded(rec_bytes) +
+           (size_t)slots_for(n_prefix) * entry_words(rec_bytes);
+}
+
+static size_t match_smem_bytes(uint32_t n_prefix, uint32_t rec_bytes) {
+    return (image_words(n_prefix, rec_bytes) + n_prefix) * sizeof(uint32_t);
 }
 
 template <int NCHUNK, bool WIDE>
@@ -193,7 +257,8 @@ static int launch_match(const void *d_heads, uint64_t n_keys, const void *d_tbl,
     const uint32_t n_slots = slots_for(n_prefix);
     uint32_t log2_slots = 0;
     while ((1u << log2_slots) < n_slots) ++log2_slots;
-    const size_t smem = match_smem_bytes(n_prefix, n_slots, rec_bytes);
+    const size_t smem = match_smem_bytes(n_prefix, rec_bytes);
+    if (smem > kMaxMatchSmem) return KAS_ERR_UNSUPPORTED;
     auto kern = match_count_kernel<NCHUNK, WIDE>;
     if (smem > 48 * 1024)
         KAS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -250,26 +315,26 @@ uint32_t kas_rec_bytes_for(uint32_t max_name_len) {
 size_t kas_prefix_table_bytes(uint32_t n_prefix, uint32_t rec_bytes) {
     if (n_prefix == 0 || n_prefix > KAS_MAX_PREFIXES) return 0;
     if (rec_bytes == 0 || rec_bytes % 16 || rec_bytes > KAS_MAX_REC_BYTES) return 0;
-    return (kTableHeaderWords + (size_t)(region_words(rec_bytes) + 1) * slots_for(n_prefix)) * sizeof(uint32_t);
+    if (match_smem_bytes(n_prefix, rec_bytes) > kMaxMatchSmem) return 0;
+    return (kTableHeaderWords + image_words(n_prefix, rec_bytes)) * sizeof(uint32_t);
 }
 
 int kas_prefix_table_build(const uint8_t *names, const uint32_t *name_off, uint32_t n_prefix,
                            uint32_t rec_bytes, void *host_tbl, size_t tbl_bytes) {
     if (!name_off || !host_tbl || (!names && n_prefix && name_off[n_prefix] != 0)) return KAS_ERR_INVALID;
+    if (n_prefix == 0 || n_prefix > KAS_MAX_PREFIXES) return KAS_ERR_INVALID;
     const size_t need = kas_prefix_table_bytes(n_prefix, rec_bytes);
-    if (need == 0) return n_prefix == 0 || n_prefix > KAS_MAX_PREFIXES ? KAS_ERR_INVALID : KAS_ERR_UNSUPPORTED;
+    if (need == 0) return KAS_ERR_UNSUPPORTED;
     if (tbl_bytes < need) return KAS_ERR_TOO_SMALL;
-    const uint32_t RW = region_words(rec_bytes);
+    const uint32_t RW = region_words(rec_bytes), RWP = region_words_padded(rec_bytes);
+    const uint32_t EW = entry_words(rec_bytes), rows = length_rows(rec_bytes);
     const uint32_t n_slots = slots_for(n_prefix);
     uint32_t log2_slots = 0;
     while ((1u << log2_slots) < n_slots) ++log2_slots;
-    uint32_t *t = static_cast<uint32_t *>(host_tbl);
-    memset(t, 0, need);
-    uint64_t len_mask = 0;
-    uint32_t *words = t + kTableHeaderWords;
-    uint32_t *qid = words + (size_t)RW * n_slots;
-    for (uint32_t i = 0; i < n_slots; ++i) qid[i] = kNoQueue;
-    std::vector<std::string> seen;
+
+    // entries: every name + ":" and every cut of it after an inner colon
+    struct Entry { uint32_t q; bool ext; };
+    std::map<std::string, Entry> entries;
     for (uint32_t q = 0; q < n_prefix; ++q) {
         if (name_off[q + 1] < name_off[q]) return KAS_ERR_INVALID;
         const uint32_t len = name_off[q + 1] - name_off[q];
@@ -281,26 +346,48 @@ int kas_prefix_table_build(const uint8_t *names, const uint32_t *name_off, uint3
             if (c == 0) return KAS_ERR_UNSUPPORTED;
         }
         std::string s(reinterpret_cast<const char *>(nm), len);
-        for (const auto &o : seen)
-            if (o == s) return KAS_ERR_INVALID;  // redis_keys is a dict: names are unique
-        seen.push_back(s);
-        uint8_t buf[KAS_MAX_REC_BYTES + 4] = {0};
-        memcpy(buf, nm, len);
-        buf[len] = ':';
-        const uint32_t nbytes = len + 1;
+        s.push_back(':');
+        auto it = entries.find(s);
+        if (it != entries.end() && it->second.q != kVirtualQueue) return KAS_ERR_INVALID;  // duplicate name
+        if (it == entries.end()) entries[s] = Entry{q, false};
+        else it->second.q = q;
+        for (uint32_t i = 0; i < len; ++i) {
+            if (nm[i] != ':') continue;
+            std::string cut(reinterpret_cast<const char *>(nm), i + 1);   // includes the inner colon
+            auto jt = entries.find(cut);
+            if (jt == entries.end()) entries[cut] = Entry{kVirtualQueue, true};
+            else jt->second.ext = true;
+        }
+    }
+    if (entries.size() * 4 > (size_t)n_slots * 3) return KAS_ERR_UNSUPPORTED;   // too many nested cuts
+
+    uint32_t *t = static_cast<uint32_t *>(host_tbl);
+    memset(t, 0, need);
+    uint32_t *masks = t + kTableHeaderWords;
+    uint32_t *slots = masks + (size_t)rows * RWP;
+    for (uint32_t L = 0; L < rows; ++L)
+        for (uint32_t k = 0; k < RW; ++k) masks[(size_t)L * RWP + k] = word_mask((int)k, (int)L + 1);
+    uint64_t len_mask = 0;
+    for (const auto &kv : entries) {
+        const std::string &s = kv.first;
+        const uint32_t nbytes = (uint32_t)s.size();
+        uint8_t buf[KAS_MAX_REC_BYTES + 8] = {0};
+        memcpy(buf, s.data(), nbytes);
         uint32_t m[(KAS_MAX_REC_BYTES + 3) / 4];
-        uint32_t h = hash_init(nbytes);
+        uint32_t h = 0;
         for (uint32_t k = 0; k < RW; ++k) {
             m[k] = (uint32_t)buf[4 * k] | ((uint32_t)buf[4 * k + 1] << 8) |
                    ((uint32_t)buf[4 * k + 2] << 16) | ((uint32_t)buf[4 * k + 3] << 24);
-            m[k] &= word_mask((int)k, (int)nbytes);
-            h = hash_step(h, m[k]);
+            h += m[k] * hash_word_constant((int)k);
         }
-        uint32_t slot = hash_slot(h, log2_slots);
-        while (words[slot] != 0u) slot = (slot + 1) & (n_slots - 1);
-        for (uint32_t k = 0; k < RW; ++k) words[(size_t)k * n_slots + slot] = m[k];
-        qid[slot] = q;
-        len_mask |= 1ull << len;
+        const uint32_t tag = hash_finish(h, nbytes);
+        uint32_t slot = hash_slot(tag, 32u - log2_slots);
+        while (slots[(size_t)slot * EW + RW] != 0u) slot = (slot + 1) & (n_slots - 1);
+        uint32_t *e = slots + (size_t)slot * EW;
+        for (uint32_t k = 0; k < RW; ++k) e[k] = m[k];
+        e[RW] = tag;
+        e[RW + 1] = kv.second.q | (kv.second.ext ? kExtFlag : 0u);
+        len_mask |= 1ull << (nbytes - 1);
     }
     t[0] = kTableMagic;
     t[1] = rec_bytes;
@@ -308,7 +395,7 @@ int kas_prefix_table_build(const uint8_t *names, const uint32_t *name_off, uint3
     t[3] = n_slots;
     t[4] = (uint32_t)len_mask;
     t[5] = (uint32_t)(len_mask >> 32);
-    t[6] = RW;
+    t[6] = EW;
     t[7] = log2_slots;
     return KAS_OK;
 }

@@ -12,12 +12,13 @@
 #include "kas_common.cuh"
 
 #include <limits.h>
+#include <type_traits>
 
 namespace kas {
 
 constexpr int kReplayThreads = 128;
 constexpr int kMaxPoliciesPerLaunch = 32;
-constexpr int kTickUnroll = 8;
+constexpr int kTickUnroll = 4;
 
 struct PolDev {
     uint64_t magic;  // ceil(2^64 / |kpp|); 0 when |kpp| == 1
@@ -63,17 +64,42 @@ __device__ __forceinline__ int64_t floordiv_any(int64_t tally, const PolDev &p) 
     return (int64_t)q ^ s;
 }
 
-// get_desired_pods (autoscaler.py:215-219) for one queue.
-template <bool GENERIC>
-__device__ __forceinline__ int32_t decide(int32_t llen, int32_t inprog, const PolDev &p, int32_t cur) {
-    if (!GENERIC && ((llen | inprog) >= 0)) {
-        // kpp >= 1 and a non-negative tally < 2^32: 32-bit quotient by multiply-high
-        const uint32_t u = (uint32_t)llen + (uint32_t)inprog;
-        const uint32_t q = p.magic ? (uint32_t)__umul64hi(p.magic, (uint64_t)u) : u;
-        const int32_t d = (int32_t)min(q, 0x7FFFFFFFu);  // saturating keeps every comparison's outcome
-        return clip32(d, p.mn, p.mx, cur);
-    }
+// Execution modes, chosen per launch by the host from the policies alone:
+//   kGeneric  any kpp != 0, any min/max: exact 64-bit path.
+//   kSimple   every policy has kpp >= 1 and min <= max (every sane configuration):
+//             a non-negative tally needs only a 32-bit multiply-high, the if/elif
+//             clamp is max(min(d, max), min), "never scale down to a non-zero count"
+//             is d > 0 ? max(d, cur) : d, and for a single-queue resource clipping
+//             the one-term sum again (autoscaler.py:259) changes nothing.
+//   kSimpleK1 kSimple with every kpp == 1 (scale.py:92 default): no division at all.
+// Negative trace values take the exact path in every mode; all modes give the
+// reference's integers.
+enum ReplayMode { kGeneric = 0, kSimple = 1, kSimpleK1 = 2 };
+
+// get_desired_pods (autoscaler.py:215-219) for one queue, exact for any input.
+__device__ __forceinline__ int32_t decide_exact(int32_t llen, int32_t inprog, const PolDev &p, int32_t cur) {
     return clip64(floordiv_any((int64_t)llen + (int64_t)inprog, p), p.mn, p.mx, cur);
+}
+
+// The same for kpp >= 1, min <= max and a tally in [0, 2^32).
+template <bool K1>
+__device__ __forceinline__ int32_t decide_simple(uint32_t tally, const PolDev &p, int32_t cur) {
+    uint32_t q = tally;
+    if (!K1) {
+        // floor(tally / kpp) = high 64 bits of magic * tally; the quotient fits 32 bits
+        const uint32_t lo_hi = __umulhi((uint32_t)p.magic, tally);
+        q = (uint32_t)(((uint64_t)(uint32_t)(p.magic >> 32) * tally + lo_hi) >> 32);
+    }
+    int32_t d = (int32_t)min(q, 0x7FFFFFFFu);   // saturating keeps every comparison's outcome
+    d = max(min(d, p.mx), p.mn);
+    return d > 0 ? max(d, cur) : d;
+}
+
+template <int MODE>
+__device__ __forceinline__ int32_t decide(int32_t llen, int32_t inprog, const PolDev &p, int32_t cur) {
+    if (MODE != kGeneric && ((llen | inprog) >= 0))
+        return decide_simple<MODE == kSimpleK1>((uint32_t)llen + (uint32_t)inprog, p, cur);
+    return decide_exact(llen, inprog, p, cur);
 }
 
 __device__ __forceinline__ long long warp_sum_ll(long long v) {
@@ -83,15 +109,30 @@ __device__ __forceinline__ long long warp_sum_ll(long long v) {
 }
 
 // ---- every queue is its own resource (R == Q) ------------------------------
-template <int VEC, int SP, bool TICKIP, bool GENERIC>
+// IPMODE 0: no in-progress term, 1: one value per queue, 2: one per (tick, queue).
+// Blocks are numbered policy-chunk fastest, so the chunks that read the same
+// trace columns run together and share them through L2.
+template <int VEC, int SP, int IPMODE, int MODE>
 __global__ void __launch_bounds__(kReplayThreads)
 replay_identity_kernel(const __grid_constant__ ReplayParams P) {
     constexpr int U = kTickUnroll;
-    const uint64_t r0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * VEC;
+    const uint32_t ny = (P.pol_count + SP - 1) / SP;
+    const uint32_t pbase = (blockIdx.x % ny) * SP;   // index into P.pol
+    const uint64_t r0 = ((uint64_t)(blockIdx.x / ny) * blockDim.x + threadIdx.x) * VEC;
     const bool valid = r0 < P.R;
-    const uint32_t pbase = blockIdx.y * SP;   // index into P.pol
     const uint32_t T = P.T;
     const uint64_t Q = P.Q;
+
+    // this thread's policies, in registers; slots past the end repeat the last policy
+    // and are never written out
+    PolDev pol[SP];
+    bool live[SP];
+#pragma unroll
+    for (int s = 0; s < SP; ++s) {
+        live[s] = pbase + s < P.pol_count;
+        pol[s] = P.pol[live[s] ? pbase + s : P.pol_count - 1];
+    }
+    const bool dense = P.dense != nullptr;
 
     int32_t cur[SP][VEC];
     long long pt[SP][VEC];
@@ -100,62 +141,92 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
 #pragma unroll
     for (int v = 0; v < VEC; ++v) {
         const int32_t c0 = (valid && P.cur0) ? P.cur0[r0 + v] : 0;
-        ipq[v] = (valid && P.inprog_mode == 1) ? P.inprog[r0 + v] : 0;
+        ipq[v] = (valid && IPMODE == 1) ? P.inprog[r0 + v] : 0;
 #pragma unroll
         for (int s = 0; s < SP; ++s) { cur[s][v] = c0; pt[s][v] = 0; np[s][v] = 0u; }
     }
 
     if (valid) {
         const int32_t *lrow = P.llen + r0;
-        const int32_t *irow = TICKIP ? P.inprog + r0 : nullptr;
-        auto step = [&](uint32_t t, const int32_t (&l)[VEC], const int32_t (&ip)[VEC]) {
+        const int32_t *irow = IPMODE == 2 ? P.inprog + r0 : nullptr;
+        // one tick of VEC resources under SP policies; FASTOK: no negative input in sight
+        auto step = [&](uint32_t t, const int32_t (&l)[VEC], const int32_t (&ip)[VEC], auto fastok) {
+            constexpr bool FASTOK = decltype(fastok)::value;
 #pragma unroll
             for (int s = 0; s < SP; ++s) {
-                if (pbase + s < P.pol_count) {
-                    const PolDev &p = P.pol[pbase + s];
 #pragma unroll
-                    for (int v = 0; v < VEC; ++v) {
-                        const int32_t c = cur[s][v];
-                        const int32_t d = decide<GENERIC>(l[v], ip[v], p, c);     // :255-257
-                        const int32_t want = clip32(d, p.mn, p.mx, c);            // :259
-                        np[s][v] += (want != c);                                  // :227
-                        cur[s][v] = want;
-                        pt[s][v] += want;
+                for (int v = 0; v < VEC; ++v) {
+                    const int32_t c = cur[s][v];
+                    int32_t want;
+                    if constexpr (FASTOK && MODE != kGeneric) {
+                        const uint32_t tally = (uint32_t)l[v] + (IPMODE == 0 ? 0u : (uint32_t)ip[v]);
+                        want = decide_simple<MODE == kSimpleK1>(tally, pol[s], c);        // :255-259
+                    } else {
+                        want = decide_exact(l[v], IPMODE == 0 ? 0 : ip[v], pol[s], c);    // :255-257
+                        want = clip32(want, pol[s].mn, pol[s].mx, c);                     // :259
                     }
-                    if (P.dense) {
-                        int32_t *o = P.dense + ((uint64_t)(P.pol_first + pbase + s) * T + t) * P.R + r0;
-                        if constexpr (VEC == 4)
-                            *reinterpret_cast<int4 *>(o) = make_int4(cur[s][0], cur[s][1], cur[s][2], cur[s][3]);
-                        else
-                            o[0] = cur[s][0];
-                    }
+                    np[s][v] += (want != c);                                              // :227
+                    cur[s][v] = want;
+                    pt[s][v] += want;
+                }
+                if (dense && live[s]) {
+                    int32_t *o = P.dense + ((uint64_t)(P.pol_first + pbase + s) * T + t) * P.R + r0;
+                    if constexpr (VEC == 4)
+                        *reinterpret_cast<int4 *>(o) = make_int4(cur[s][0], cur[s][1], cur[s][2], cur[s][3]);
+                    else
+                        o[0] = cur[s][0];
                 }
             }
         };
-        uint32_t t0 = 0;
-        for (; t0 + U <= T; t0 += U) {
-            int32_t l[U][VEC], ip[U][VEC];
+        // rows t .. t+U-1 (clamped to the last tick) into registers
+        auto load = [&](uint32_t t, int32_t (&l)[U][VEC], int32_t (&ip)[U][VEC]) {
 #pragma unroll
             for (int u = 0; u < U; ++u) {
-                const uint64_t o = (uint64_t)(t0 + u) * Q;
+                const uint32_t tt = min(t + (uint32_t)u, T - 1);
+                const uint64_t o = (uint64_t)tt * Q;
                 if constexpr (VEC == 4) {
                     const int4 a = ldg_stream_i4(lrow + o);
                     l[u][0] = a.x; l[u][1] = a.y; l[u][2] = a.z; l[u][3] = a.w;
-                    if constexpr (TICKIP) {
+                    if constexpr (IPMODE == 2) {
                         const int4 b = ldg_stream_i4(irow + o);
                         ip[u][0] = b.x; ip[u][1] = b.y; ip[u][2] = b.z; ip[u][3] = b.w;
                     }
                 } else {
                     l[u][0] = ldg_stream_i32(lrow + o);
-                    if constexpr (TICKIP) ip[u][0] = ldg_stream_i32(irow + o);
+                    if constexpr (IPMODE == 2) ip[u][0] = ldg_stream_i32(irow + o);
                 }
-                if constexpr (!TICKIP) {
+                if constexpr (IPMODE != 2) {
 #pragma unroll
                     for (int v = 0; v < VEC; ++v) ip[u][v] = ipq[v];
                 }
             }
+        };
+        // U ticks from registers; one sign test for the whole chunk picks the path
+        auto run = [&](uint32_t t, const int32_t (&l)[U][VEC], const int32_t (&ip)[U][VEC]) {
+            int32_t any = 0;
 #pragma unroll
-            for (int u = 0; u < U; ++u) step(t0 + u, l[u], ip[u]);
+            for (int u = 0; u < U; ++u)
+#pragma unroll
+                for (int v = 0; v < VEC; ++v) any |= l[u][v] | (IPMODE == 0 ? 0 : ip[u][v]);
+            if (MODE != kGeneric && any >= 0) {
+#pragma unroll
+                for (int u = 0; u < U; ++u) step(t + u, l[u], ip[u], std::true_type{});
+            } else {
+#pragma unroll
+                for (int u = 0; u < U; ++u) step(t + u, l[u], ip[u], std::false_type{});
+            }
+        };
+        // software pipeline: the next U rows are in flight while U rows are consumed
+        int32_t la[U][VEC], ia[U][VEC], lb[U][VEC], ib[U][VEC];
+        uint32_t t0 = 0;
+        if (T >= 2 * U) {
+            load(0, la, ia);
+            for (; t0 + 2 * U <= T; t0 += 2 * U) {
+                load(t0 + U, lb, ib);
+                run(t0, la, ia);
+                load(t0 + 2 * U, la, ia);
+                run(t0 + U, lb, ib);
+            }
         }
         for (; t0 < T; ++t0) {
             int32_t l[VEC], ip[VEC];
@@ -163,14 +234,14 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
 #pragma unroll
             for (int v = 0; v < VEC; ++v) {
                 l[v] = ldg_stream_i32(lrow + o + v);
-                ip[v] = TICKIP ? ldg_stream_i32(irow + o + v) : ipq[v];
+                ip[v] = IPMODE == 2 ? ldg_stream_i32(irow + o + v) : ipq[v];
             }
-            step(t0, l, ip);
+            step(t0, l, ip, std::false_type{});
         }
         if (P.totals) {
 #pragma unroll
             for (int s = 0; s < SP; ++s)
-                if (pbase + s < P.pol_count)
+                if (live[s])
 #pragma unroll
                     for (int v = 0; v < VEC; ++v) {
                         kas_totals o;
@@ -184,7 +255,7 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
     if (P.sums) {
 #pragma unroll
         for (int s = 0; s < SP; ++s) {
-            if (pbase + s < P.pol_count) {   // uniform across the block
+            if (live[s]) {   // uniform across the block
                 long long a = 0, b = 0, c = 0;
                 if (valid) {
 #pragma unroll
@@ -203,12 +274,13 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
 }
 
 // ---- resources that own several queues (CSR groups) ------------------------
-template <int SP, bool GENERIC>
+template <int SP, int MODE>
 __global__ void __launch_bounds__(kReplayThreads)
 replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
-    const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t ny = (P.pol_count + SP - 1) / SP;
+    const uint32_t pbase = (blockIdx.x % ny) * SP;
+    const uint64_t r = (uint64_t)(blockIdx.x / ny) * blockDim.x + threadIdx.x;
     const bool valid = r < P.R;
-    const uint32_t pbase = blockIdx.y * SP;
     const uint32_t T = P.T;
     const uint64_t Q = P.Q;
     int32_t cur[SP];
@@ -232,7 +304,7 @@ replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
 #pragma unroll
                 for (int s = 0; s < SP; ++s)
                     if (pbase + s < P.pol_count)
-                        sum[s] += decide<GENERIC>(l, ip, P.pol[pbase + s], cur[s]);   // :255-257
+                        sum[s] += decide<MODE>(l, ip, P.pol[pbase + s], cur[s]);   // :255-257
             }
 #pragma unroll
             for (int s = 0; s < SP; ++s) {
@@ -336,19 +408,31 @@ synth_trace_kernel(uint64_t seed, uint32_t T, uint64_t q_first, uint64_t n_q, in
     }
 }
 
-template <int VEC, int SP, bool TICKIP>
-static void launch_identity(const ReplayParams &P, bool generic, cudaStream_t stream) {
+template <int VEC, int SP>
+static void launch_identity(const ReplayParams &P, int mode, cudaStream_t stream) {
     const uint64_t threads = (P.R + VEC - 1) / VEC;
-    dim3 grid((unsigned)((threads + kReplayThreads - 1) / kReplayThreads), (P.pol_count + SP - 1) / SP);
-    if (generic) replay_identity_kernel<VEC, SP, TICKIP, true><<<grid, kReplayThreads, 0, stream>>>(P);
-    else replay_identity_kernel<VEC, SP, TICKIP, false><<<grid, kReplayThreads, 0, stream>>>(P);
+    const uint64_t nx = (threads + kReplayThreads - 1) / kReplayThreads;
+    const uint32_t ny = (P.pol_count + SP - 1) / SP;
+    const unsigned grid = (unsigned)(nx * ny);
+#define KAS_LAUNCH_ID(IPM)                                                                        \
+    do {                                                                                          \
+        if (mode == kSimpleK1) replay_identity_kernel<VEC, SP, IPM, kSimpleK1><<<grid, kReplayThreads, 0, stream>>>(P); \
+        else if (mode == kSimple) replay_identity_kernel<VEC, SP, IPM, kSimple><<<grid, kReplayThreads, 0, stream>>>(P); \
+        else replay_identity_kernel<VEC, SP, IPM, kGeneric><<<grid, kReplayThreads, 0, stream>>>(P);     \
+    } while (0)
+    if (P.inprog_mode == 0) KAS_LAUNCH_ID(0);
+    else if (P.inprog_mode == 1) KAS_LAUNCH_ID(1);
+    else KAS_LAUNCH_ID(2);
+#undef KAS_LAUNCH_ID
 }
 
 template <int SP>
-static void launch_grouped(const ReplayParams &P, bool generic, cudaStream_t stream) {
-    dim3 grid((unsigned)((P.R + kReplayThreads - 1) / kReplayThreads), (P.pol_count + SP - 1) / SP);
-    if (generic) replay_grouped_kernel<SP, true><<<grid, kReplayThreads, 0, stream>>>(P);
-    else replay_grouped_kernel<SP, false><<<grid, kReplayThreads, 0, stream>>>(P);
+static void launch_grouped(const ReplayParams &P, int mode, cudaStream_t stream) {
+    const uint64_t nx = (P.R + kReplayThreads - 1) / kReplayThreads;
+    const uint32_t ny = (P.pol_count + SP - 1) / SP;
+    const unsigned grid = (unsigned)(nx * ny);
+    if (mode != kGeneric) replay_grouped_kernel<SP, kSimple><<<grid, kReplayThreads, 0, stream>>>(P);
+    else replay_grouped_kernel<SP, kGeneric><<<grid, kReplayThreads, 0, stream>>>(P);
 }
 
 }  // namespace kas
@@ -365,15 +449,17 @@ int kas_replay(const kas_replay_args *a, void *stream_v) {
     if (a->inprog_mode != 0 && !a->d_inprog) return KAS_ERR_INVALID;
     if (!a->d_group_off && a->n_resources != a->n_queues) return KAS_ERR_INVALID;
     if (!a->d_totals && !a->d_sums && !a->d_dense) return KAS_ERR_INVALID;
-    if (a->n_resources > 0x7FFFFFFFull * kReplayThreads) return KAS_ERR_UNSUPPORTED;
+    if (a->n_resources > (0x7FFFFFFFull / kMaxPoliciesPerLaunch) * kReplayThreads) return KAS_ERR_UNSUPPORTED;
     if (!aligned(a->d_llen, 4) || !aligned(a->d_inprog, 4) || !aligned(a->d_dense, 4) ||
         !aligned(a->d_totals, 8) || !aligned(a->d_sums, 8) || !aligned(a->d_group_off, 8) ||
         !aligned(a->d_cur0, 4))
         return KAS_ERR_ALIGNMENT;
-    bool generic = false;
+    int mode = kSimpleK1;
     for (uint32_t s = 0; s < a->n_policies; ++s) {
-        if (a->policies[s].keys_per_pod == 0) return KAS_ERR_ZERO_DIVISION;
-        if (a->policies[s].keys_per_pod < 0) generic = true;
+        const kas_policy &p = a->policies[s];
+        if (p.keys_per_pod == 0) return KAS_ERR_ZERO_DIVISION;
+        if (p.keys_per_pod < 0 || p.min_pods > p.max_pods) mode = kGeneric;
+        else if (p.keys_per_pod != 1 && mode == kSimpleK1) mode = kSimple;
     }
     cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
     if (a->d_sums)
@@ -381,6 +467,7 @@ int kas_replay(const kas_replay_args *a, void *stream_v) {
 
     const bool identity = a->d_group_off == nullptr;
     const bool tickip = a->inprog_mode == 2;
+    if (a->n_ticks == 0) return KAS_ERR_INVALID;
     const bool vec4 = identity && (a->n_queues % 4 == 0) && aligned(a->d_llen, 16) &&
                       (!tickip || aligned(a->d_inprog, 16)) &&
                       (a->inprog_mode != 1 || aligned(a->d_inprog, 4)) &&
@@ -418,19 +505,15 @@ int kas_replay(const kas_replay_args *a, void *stream_v) {
         }
         if (identity) {
             if (P.pol_count == 1) {
-                if (vec4) tickip ? launch_identity<4, 1, true>(P, generic, stream)
-                                 : launch_identity<4, 1, false>(P, generic, stream);
-                else tickip ? launch_identity<1, 1, true>(P, generic, stream)
-                            : launch_identity<1, 1, false>(P, generic, stream);
+                if (vec4) launch_identity<4, 1>(P, mode, stream);
+                else launch_identity<1, 1>(P, mode, stream);
             } else {
-                if (vec4) tickip ? launch_identity<4, 4, true>(P, generic, stream)
-                                 : launch_identity<4, 4, false>(P, generic, stream);
-                else tickip ? launch_identity<1, 4, true>(P, generic, stream)
-                            : launch_identity<1, 4, false>(P, generic, stream);
+                if (vec4) launch_identity<4, 4>(P, mode, stream);
+                else launch_identity<1, 4>(P, mode, stream);
             }
         } else {
-            if (P.pol_count == 1) launch_grouped<1>(P, generic, stream);
-            else launch_grouped<4>(P, generic, stream);
+            if (P.pol_count == 1) launch_grouped<1>(P, mode, stream);
+            else launch_grouped<4>(P, mode, stream);
         }
         KAS_CUDA_TRY(cudaGetLastError());
     }

@@ -3,17 +3,27 @@
 //
 // A key matches queue q iff it starts with "processing-" + name_q + ":"
 // (autoscaler.py:69 with a literal name).  Bytes 11.. of a record are the
-// "region"; a candidate is a ':' found at region offset L, the candidate
-// string is region[0..L] INCLUDING the colon, and the table maps such strings
-// to queue ids by open addressing.
+// "region".  The kernel walks the ':' bytes of the region in order; at a ':'
+// at region offset L the candidate string is region[0..L] INCLUDING the colon,
+// and the table maps such strings to entries by open addressing.
+//
+// The table is closed under "cut at an inner colon": for a name "a:b:c" the
+// strings "a:" and "a:b:" are entries too (virtual ones, with no queue id) and
+// carry an `ext` flag saying that a longer entry continues them.  So the walk
+// can stop at the first colon whose candidate is not an entry, or whose entry
+// has no continuation: nothing longer can match.  Nested queue names (a key
+// counts for "predict" and for "predict:zstack") fall out of the same walk.
 //
 // Device image (uint32 words):
 //   [0] magic  [1] rec_bytes  [2] n_prefix  [3] n_slots (power of two)
-//   [4] len_mask_lo  [5] len_mask_hi   (bit L set <=> some name has length L)
-//   [6] region_words RW  [7] log2(n_slots)
-//   then RW arrays of n_slots words: word k of every slot (SoA, so that lanes
-//   probing different slots hit different banks), then n_slots queue ids.
-//   An empty slot has word 0 == 0 (a stored string always holds its ':').
+//   [4] len_mask_lo  [5] len_mask_hi   (bit L set <=> some entry has name length L)
+//   [6] entry_words EW  [7] log2(n_slots)
+//   length masks: (rec_bytes-11) rows of RWP words; row L holds, for each region
+//       word, the mask of the bytes below L+1 (RWP = region words rounded up to 4)
+//   entries: n_slots rows of EW words: RW region words (masked, zero padded),
+//       tag (finalised hash | 1; 0 = empty slot), meta (queue id | ext << 31,
+//       queue id 0x7FFFFFFF = virtual).  EW = RW + 2 is a multiple of 4, so a row
+//       is read with 128-bit shared loads.
 #pragma once
 #include <stdint.h>
 
@@ -25,11 +35,16 @@
 
 namespace kas {
 
-constexpr uint32_t kTableMagic = 0x4B415331u;  // "KAS1"
+constexpr uint32_t kTableMagic = 0x4B415332u;  // "KAS2"
 constexpr uint32_t kTableHeaderWords = 8;
 constexpr uint32_t kLiteralLen = 11;           // strlen("processing-")
+constexpr uint32_t kVirtualQueue = 0x7FFFFFFFu;
+constexpr uint32_t kExtFlag = 0x80000000u;
 
 KAS_HD constexpr uint32_t region_words(uint32_t rec_bytes) { return (rec_bytes - kLiteralLen + 3) / 4; }
+KAS_HD constexpr uint32_t region_words_padded(uint32_t rec_bytes) { return (region_words(rec_bytes) + 3) / 4 * 4; }
+KAS_HD constexpr uint32_t entry_words(uint32_t rec_bytes) { return region_words(rec_bytes) + 2; }
+KAS_HD constexpr uint32_t length_rows(uint32_t rec_bytes) { return rec_bytes - kLiteralLen; }
 
 // Mask selecting the bytes of little-endian region word k that lie below nbytes.
 KAS_HD uint32_t word_mask(int k, int nbytes) {
@@ -37,15 +52,17 @@ KAS_HD uint32_t word_mask(int k, int nbytes) {
     return rem >= 4 ? 0xFFFFFFFFu : (rem <= 0 ? 0u : (0xFFFFFFFFu >> (32 - 8 * rem)));
 }
 
-KAS_HD uint32_t hash_step(uint32_t h, uint32_t w) {
-    h ^= w;
-    h *= 0x9E3779B1u;
-    return h ^ (h >> 15);
-}
-KAS_HD uint32_t hash_init(uint32_t nbytes) { return nbytes * 0x85EBCA6Bu + 0x27D4EB2Fu; }
-KAS_HD uint32_t hash_slot(uint32_t h, uint32_t log2_slots) {
+// Hash of the masked region words: a multiply-add chain (IMAD on the device)
+// with one odd constant per word, then a finaliser.  `tag` is never 0.
+KAS_HD uint32_t hash_word_constant(int k) { return 0x9E3779B1u + 0x3C6EF372u * (uint32_t)k; }
+KAS_HD uint32_t hash_finish(uint32_t h, uint32_t nbytes) {
+    h += nbytes * 0x85EBCA6Bu;
+    h ^= h >> 15;
     h *= 0xC2B2AE35u;
-    return log2_slots ? (h >> (32 - log2_slots)) : 0u;
+    h ^= h >> 13;
+    return h | 1u;
 }
+// slot_shift = 32 - log2(n_slots); n_slots >= 8, so the shift is below 32
+KAS_HD uint32_t hash_slot(uint32_t tag, uint32_t slot_shift) { return (tag * 0x27D4EB2Fu) >> slot_shift; }
 
 }  // namespace kas
