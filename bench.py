@@ -334,6 +334,8 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_ms = float(t.item())
     e2e_ok = bool((out_host.numpy() == counts_box).all())
+    if not e2e_ok:
+        raise SystemExit('bench.py: end-to-end counts differ from the resident-data counts')
     e2e = {'value': world * n / (e2e_ms * 1e-3), 'unit': 'keys/s', 'h2d_bytes_per_step': n * W,
            'd2h_bytes_per_step': 8 * N_PREFIX, 'ms_per_step': e2e_ms, 'steps': e2e_steps,
            'matches_resident_result': e2e_ok,
@@ -398,6 +400,9 @@ def run_ours(args):
         # the same sample through the GPU path must give the same counts
         c = engine.match_count(d_heads, n_sample, W, table, N_PREFIX)
         agree = bool((engine.counts_to_host(c).astype(np.int64) == ccounts.astype(np.int64)).all())
+        if not agree:
+            raise SystemExit('bench.py: GPU counts differ from the CPU oracle on the sample -- '
+                             'a throughput number for wrong results is not a result')
         prate, pdt = cpu_python_port_sample(20_000)
         cpu = {'value': rate, 'unit': 'keys/s', 'cores': threads, 'kind': 'port',
                'sample': '%d keys x %d queues of the same keyspace, C restatement, one full pass '

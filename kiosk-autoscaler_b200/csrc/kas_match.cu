@@ -17,6 +17,7 @@
 #include "kas_table.h"
 
 #include <string.h>
+#include <algorithm>
 #include <map>
 #include <type_traits>
 #include <string>
@@ -24,6 +25,12 @@
 
 namespace kas {
 
+#ifndef KAS_MATCH_U
+#define KAS_MATCH_U 4      // keys per thread per step (32-byte records)
+#endif
+#ifndef KAS_MATCH_MINB
+#define KAS_MATCH_MINB 4   // resident blocks per SM the register budget is held to
+#endif
 constexpr int kMatchThreads = 256;
 constexpr uint32_t kNoQueue = 0xFFFFFFFFu;
 constexpr size_t kMaxMatchSmem = 200 * 1024;
@@ -45,43 +52,47 @@ struct MatchCfg {
     static constexpr int kRWP = (kRW + 3) / 4 * 4;                         // padded to 128-bit rows
     static constexpr int kEW = kRW + 2;                                    // entry words
     static constexpr int kRows = 16 * NCHUNK - (int)kLiteralLen;           // name lengths 0..W-12
-    static constexpr int kKeysPerThread = NCHUNK <= 2 ? 4 : 2;
+    static constexpr int kKeysPerThread = NCHUNK <= 2 ? KAS_MATCH_U : 2;
     using mask_t = typename std::conditional<(kRows <= 32), uint32_t, uint64_t>::type;   // one bit per name length
+    // a deferred walk: region words + the colons still to visit, padded to 128-bit rows
+    static constexpr int kItemWords = (kRW + (int)(sizeof(mask_t) / 4) + 3) / 4 * 4;
     static_assert(kEW % 4 == 0, "entry rows must be 128-bit multiples");
 };
+constexpr int kQueueItems = 64;   // per warp: at most 31 waiting + 32 pushed by one step
 
 struct MatchSmem {
     const uint32_t *masks;    // [kRows][kRWP]
     const uint32_t *entries;  // [n_slots][kEW]
     uint32_t *hist;           // [n_prefix]
+    uint32_t *queue;          // this warp's [kQueueItems][kItemWords]
 };
 
-// Examine one record held in registers.  Returns the id of the first queue it
-// counts for (kNoQueue if none); further queues of the same key (nested names
-// such as "predict" and "predict:zstack") are added to the block histogram
-// directly, they are rare.
 template <typename M> __device__ __forceinline__ int first_bit(M m);
 template <> __device__ __forceinline__ int first_bit<uint32_t>(uint32_t m) { return __ffs((int)m) - 1; }
 template <> __device__ __forceinline__ int first_bit<uint64_t>(uint64_t m) { return __ffsll((long long)m) - 1; }
 
 template <int NCHUNK>
-__device__ __forceinline__ uint32_t match_one(const uint32_t (&x)[4 * NCHUNK], const MatchSmem &sm,
-                                              uint32_t slot_mask, uint32_t slot_shift,
-                                              typename MatchCfg<NCHUNK>::mask_t len_mask) {
+struct Matcher {
     using Cfg = MatchCfg<NCHUNK>;
     using mask_t = typename Cfg::mask_t;
-    constexpr int XW = Cfg::kRecWords, RW = Cfg::kRW, RWP = Cfg::kRWP, EW = Cfg::kEW;
-    // "processing-" = 70 72 6f 63 | 65 73 73 69 | 6e 67 2d
-    const bool literal = (x[0] == 0x636F7270u) & (x[1] == 0x69737365u) &
-                         ((x[2] & 0x00FFFFFFu) == 0x002D676Eu);
-    uint32_t first = kNoQueue;
-    if (literal) {
-        uint32_t r[RW];
+    static constexpr int XW = Cfg::kRecWords, RW = Cfg::kRW, RWP = Cfg::kRWP, EW = Cfg::kEW,
+                         IW = Cfg::kItemWords;
+    MatchSmem sm;
+    uint32_t seed, slot_shift, lane, lanemask_lt;
+    bool two_slot;
+    mask_t len_mask;
+    uint32_t waiting;   // deferred walks in this warp's queue (warp-uniform)
+
+    // Region words (bytes 11.. of the record) and the ':' positions that can end an
+    // entry.  Returns false when the record does not start with "processing-".
+    __device__ __forceinline__ bool prepare(const uint32_t (&x)[XW], uint32_t (&r)[RW], mask_t &colons) const {
+        // "processing-" = 70 72 6f 63 | 65 73 73 69 | 6e 67 2d
+        const bool literal = (x[0] == 0x636F7270u) & (x[1] == 0x69737365u) &
+                             ((x[2] & 0x00FFFFFFu) == 0x002D676Eu);
 #pragma unroll
         for (int k = 0; k < RW; ++k)
             r[k] = (3 + k < XW) ? __byte_perm(x[2 + k], x[3 + k], 0x6543) : (x[2 + k] >> 24);
-        // bit L of `colons` <=> region byte L is ':'
-        mask_t colons = 0;
+        colons = 0;   // bit L <=> region byte L is ':'
         if constexpr (sizeof(mask_t) == 4) {
 #pragma unroll
             for (int k = RW - 1; k >= 0; --k)
@@ -95,64 +106,133 @@ __device__ __forceinline__ uint32_t match_one(const uint32_t (&x)[4 * NCHUNK], c
         // others up front is safe because the table is closed under cutting at inner
         // colons: a candidate that spans a colon at a non-entry length is no entry.
         colons &= len_mask;
-        while (colons) {
+        return literal;
+    }
+
+    // Is region[0..L] an entry?  One look at its home slot (two for a two-slot
+    // table), no probing (kas_table.h).  Returns the entry's meta word, or
+    // kNoQueue when it is not an entry.
+    __device__ __forceinline__ uint32_t lookup(const uint32_t (&r)[RW], int L) const {
+        uint32_t m[RWP];
+        const uint4 *mrow = reinterpret_cast<const uint4 *>(sm.masks + (uint32_t)L * RWP);
+#pragma unroll
+        for (int j = 0; j < RWP / 4; ++j) {
+            const uint4 v = mrow[j];
+            m[4 * j] = v.x; m[4 * j + 1] = v.y; m[4 * j + 2] = v.z; m[4 * j + 3] = v.w;
+        }
+        uint32_t h = 0;
+#pragma unroll
+        for (int k = 0; k < RW; ++k) {
+            m[k] &= r[k];
+            h += m[k] * hash_word_constant(k);
+        }
+        const uint32_t tag = hash_finish(h, (uint32_t)L + 1u, seed);
+        uint32_t w[EW];
+        auto fetch = [&](uint32_t slot) {
+            const uint4 *e = reinterpret_cast<const uint4 *>(sm.entries + slot * EW);
+#pragma unroll
+            for (int j = 0; j < EW / 4; ++j) {
+                const uint4 v = e[j];
+                w[4 * j] = v.x; w[4 * j + 1] = v.y; w[4 * j + 2] = v.z; w[4 * j + 3] = v.w;
+            }
+            uint32_t diff = 0;
+#pragma unroll
+            for (int k = 0; k < RW; ++k) diff |= w[k] ^ m[k];
+            return diff == 0u;
+        };
+        bool hit = fetch(hash_slot_a(tag, slot_shift));
+        if (two_slot && !hit) hit = fetch(hash_slot_b(tag, slot_shift));
+        return hit ? w[RW + 1] : kNoQueue;
+    }
+
+    // Nested queue names ("predict" and "predict:zstack") make a key's walk go on
+    // past its first colon.  Few lanes need that, so instead of looping in place
+    // with most of the warp idle, they park the walk in the warp's queue; the warp
+    // resumes 32 parked walks at a time with every lane busy.
+    __device__ __forceinline__ void park(bool more, const uint32_t (&r)[RW], mask_t rest) {
+        const uint32_t who = __ballot_sync(0xFFFFFFFFu, more);
+        if (who == 0u) return;
+        if (more) {
+            uint32_t *it = sm.queue + (waiting + __popc(who & lanemask_lt)) * IW;
+            uint32_t v[IW];
+#pragma unroll
+            for (int k = 0; k < IW; ++k) v[k] = 0u;
+#pragma unroll
+            for (int k = 0; k < RW; ++k) v[k] = r[k];
+            v[RW] = (uint32_t)rest;
+            if constexpr (sizeof(mask_t) == 8) v[RW + 1] = (uint32_t)((uint64_t)rest >> 32);
+#pragma unroll
+            for (int j = 0; j < IW / 4; ++j)
+                reinterpret_cast<uint4 *>(it)[j] = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        }
+        waiting += __popc(who);
+        __syncwarp();
+    }
+
+    // Resume up to 32 parked walks by one colon each.
+    __device__ __forceinline__ void resume() {
+        const uint32_t n = waiting < 32u ? waiting : 32u;
+        const bool mine = lane < n;
+        waiting -= n;
+        uint32_t r[RW];
+        mask_t rest = 0;
+        if (mine) {
+            const uint32_t *it = sm.queue + (waiting + lane) * IW;
+            uint32_t v[IW];
+#pragma unroll
+            for (int j = 0; j < IW / 4; ++j) {
+                const uint4 t = reinterpret_cast<const uint4 *>(it)[j];
+                v[4 * j] = t.x; v[4 * j + 1] = t.y; v[4 * j + 2] = t.z; v[4 * j + 3] = t.w;
+            }
+#pragma unroll
+            for (int k = 0; k < RW; ++k) r[k] = v[k];
+            rest = (mask_t)v[RW];
+            if constexpr (sizeof(mask_t) == 8) rest |= (mask_t)((uint64_t)v[RW + 1] << 32);
+        } else {
+#pragma unroll
+            for (int k = 0; k < RW; ++k) r[k] = 0u;
+        }
+        __syncwarp();   // every lane has read its item before anyone parks on top of it
+        bool more = false;
+        if (mine) {
+            const int L = first_bit<mask_t>(rest);
+            rest &= rest - 1;
+            const uint32_t meta = lookup(r, L);
+            if (meta != kNoQueue) {
+                const uint32_t q = meta & ~kExtFlag;
+                if (q != kVirtualQueue) atomicAdd(&sm.hist[q], 1u);
+                more = (meta & kExtFlag) && rest != 0;
+            }
+        }
+        park(more, r, rest);
+    }
+
+    // One record: its first colon is looked up here; the id of the queue it counts
+    // for (kNoQueue if none) is returned for the warp histogram.
+    __device__ __forceinline__ uint32_t first_step(const uint32_t (&x)[XW]) {
+        uint32_t r[RW];
+        mask_t colons;
+        const bool literal = prepare(x, r, colons);
+        uint32_t q = kNoQueue;
+        bool more = false;
+        if (literal && colons != 0) {
             const int L = first_bit<mask_t>(colons);
             colons &= colons - 1;
-            const uint32_t nbytes = (uint32_t)L + 1u;
-            // masked region words and their hash
-            uint32_t m[RWP];
-            const uint4 *mrow = reinterpret_cast<const uint4 *>(sm.masks + (uint32_t)L * RWP);
-#pragma unroll
-            for (int j = 0; j < RWP / 4; ++j) {
-                const uint4 v = mrow[j];
-                m[4 * j] = v.x; m[4 * j + 1] = v.y; m[4 * j + 2] = v.z; m[4 * j + 3] = v.w;
+            const uint32_t meta = lookup(r, L);
+            if (meta != kNoQueue) {
+                const uint32_t id = meta & ~kExtFlag;
+                if (id != kVirtualQueue) q = id;
+                more = (meta & kExtFlag) && colons != 0;
             }
-            uint32_t h = 0;
-#pragma unroll
-            for (int k = 0; k < RW; ++k) {
-                m[k] &= r[k];
-                h += m[k] * hash_word_constant(k);
-            }
-            const uint32_t tag = hash_finish(h, nbytes);
-            uint32_t slot = hash_slot(tag, slot_shift);
-            uint32_t meta = 0;
-            bool hit = false;
-            for (;;) {
-                const uint32_t *e = sm.entries + slot * EW;
-                const uint32_t etag = e[RW];
-                if (etag == 0u) break;                     // empty slot: not an entry
-                if (etag == tag) {
-                    uint32_t w[EW];
-#pragma unroll
-                    for (int j = 0; j < EW / 4; ++j) {
-                        const uint4 v = reinterpret_cast<const uint4 *>(e)[j];
-                        w[4 * j] = v.x; w[4 * j + 1] = v.y; w[4 * j + 2] = v.z; w[4 * j + 3] = v.w;
-                    }
-                    uint32_t diff = 0;
-#pragma unroll
-                    for (int k = 0; k < RW; ++k) diff |= w[k] ^ m[k];
-                    if (diff == 0u) {
-                        meta = w[RW + 1];
-                        hit = true;
-                        break;
-                    }
-                }
-                slot = (slot + 1) & slot_mask;
-            }
-            if (!hit) break;
-            const uint32_t q = meta & ~kExtFlag;
-            if (q != kVirtualQueue) {
-                if (first == kNoQueue) first = q;
-                else atomicAdd(&sm.hist[q], 1u);
-            }
-            if (!(meta & kExtFlag)) break;                 // no longer queue name continues this one
         }
+        park(more, r, colons);
+        while (waiting >= 32u) resume();
+        return q;
     }
-    return first;
-}
+};
 
 template <int NCHUNK, bool WIDE>
-__global__ void __launch_bounds__(kMatchThreads)
+__global__ void __launch_bounds__(kMatchThreads, KAS_MATCH_MINB)
 match_count_kernel(const uint8_t *__restrict__ heads, uint64_t n_keys,
                    const uint32_t *__restrict__ tbl, uint32_t n_prefix, uint32_t n_slots,
                    uint32_t log2_slots, unsigned long long *__restrict__ counts) {
@@ -164,25 +244,30 @@ match_count_kernel(const uint8_t *__restrict__ heads, uint64_t n_keys,
 
     // Sizes come from the launch (they size the shared memory); a table image that
     // disagrees with them is reported by poisoning the counts, never by reading past it.
-    if (tbl[0] != kTableMagic || tbl[1] != 16u * NCHUNK || tbl[2] != n_prefix || tbl[3] != n_slots) {
+    if (tbl[0] != kTableMagic || tbl[1] != 16u * NCHUNK || tbl[2] != n_prefix || tbl[3] != n_slots ||
+        (tbl[7] & 0xFFu) != log2_slots) {
         if (blockIdx.x == 0)
             for (uint32_t i = threadIdx.x; i < n_prefix; i += blockDim.x) counts[i] = ~0ull;
         return;
     }
-    const typename Cfg::mask_t len_mask =
-        (typename Cfg::mask_t)((uint64_t)tbl[4] | ((uint64_t)tbl[5] << 32));
-    const uint32_t slot_shift = 32u - log2_slots;   // n_slots >= 8
     const uint32_t image_words = Cfg::kRows * Cfg::kRWP + n_slots * Cfg::kEW;
     for (uint32_t i = threadIdx.x; i < image_words; i += blockDim.x) smem[i] = tbl[kTableHeaderWords + i];
-    MatchSmem sm;
-    sm.masks = smem;
-    sm.entries = smem + Cfg::kRows * Cfg::kRWP;
-    sm.hist = smem + image_words;
-    for (uint32_t i = threadIdx.x; i < n_prefix; i += blockDim.x) sm.hist[i] = 0u;
+    Matcher<NCHUNK> mt;
+    mt.sm.masks = smem;
+    mt.sm.entries = smem + Cfg::kRows * Cfg::kRWP;
+    mt.sm.hist = smem + image_words;
+    mt.sm.queue = smem + image_words + ((n_prefix + 3u) & ~3u) +
+                  (threadIdx.x >> 5) * (kQueueItems * Cfg::kItemWords);
+    mt.len_mask = (typename Cfg::mask_t)((uint64_t)tbl[4] | ((uint64_t)tbl[5] << 32));
+    mt.slot_shift = 32u - log2_slots;   // n_slots >= 8
+    mt.seed = tbl[6];
+    mt.two_slot = (tbl[7] >> 8) & 1u;
+    mt.lane = threadIdx.x & 31u;
+    mt.lanemask_lt = (1u << mt.lane) - 1u;
+    mt.waiting = 0u;
+    for (uint32_t i = threadIdx.x; i < n_prefix; i += blockDim.x) mt.sm.hist[i] = 0u;
     __syncthreads();
 
-    const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t slot_mask = n_slots - 1;
     const uint64_t tile = (uint64_t)blockDim.x * U;
     for (uint64_t base = (uint64_t)blockIdx.x * tile; base < n_keys; base += (uint64_t)gridDim.x * tile) {
         uint32_t x[U][XW];
@@ -217,25 +302,25 @@ match_count_kernel(const uint8_t *__restrict__ heads, uint64_t n_keys,
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const uint32_t q = match_one<NCHUNK>(x[u], sm, slot_mask, slot_shift, len_mask);
-            __syncwarp();
+            const uint32_t q = mt.first_step(x[u]);
             if (__any_sync(0xFFFFFFFFu, q != kNoQueue)) {
                 // warp histogram: lanes holding the same queue elect one adder
                 const uint32_t peers = __match_any_sync(0xFFFFFFFFu, q);
-                if (q != kNoQueue && lane == (uint32_t)(__ffs(peers) - 1))
-                    atomicAdd(&sm.hist[q], (uint32_t)__popc(peers));
+                if (q != kNoQueue && (peers & mt.lanemask_lt) == 0u)
+                    atomicAdd(&mt.sm.hist[q], (uint32_t)__popc(peers));
             }
         }
     }
+    while (mt.waiting) mt.resume();
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < n_prefix; i += blockDim.x) {
-        const uint32_t c = sm.hist[i];
+        const uint32_t c = mt.sm.hist[i];
         if (c) atomicAdd(&counts[i], (unsigned long long)c);
     }
 }
 
 static uint32_t slots_for(uint32_t n_prefix) {
-    uint32_t want = n_prefix <= 256 ? 4 * n_prefix : 2 * n_prefix;
+    uint32_t want = n_prefix <= 128 ? 8 * n_prefix : (n_prefix <= 256 ? 4 * n_prefix : 2 * n_prefix + 256);
     uint32_t s = 8;
     while (s < want) s <<= 1;
     return s;
@@ -246,8 +331,14 @@ static size_t image_words(uint32_t n_prefix, uint32_t rec_bytes) {
            (size_t)slots_for(n_prefix) * entry_words(rec_bytes);
 }
 
+static uint32_t item_words(uint32_t rec_bytes) {
+    const uint32_t mask_words = length_rows(rec_bytes) <= 32 ? 1 : 2;
+    return (region_words(rec_bytes) + mask_words + 3) / 4 * 4;
+}
+
 static size_t match_smem_bytes(uint32_t n_prefix, uint32_t rec_bytes) {
-    return (image_words(n_prefix, rec_bytes) + n_prefix) * sizeof(uint32_t);
+    const size_t queues = (size_t)(kMatchThreads / 32) * kQueueItems * item_words(rec_bytes);
+    return (image_words(n_prefix, rec_bytes) + ((n_prefix + 3u) & ~3u) + queues) * sizeof(uint32_t);
 }
 
 template <int NCHUNK, bool WIDE>
@@ -359,7 +450,7 @@ int kas_prefix_table_build(const uint8_t *names, const uint32_t *name_off, uint3
             else jt->second.ext = true;
         }
     }
-    if (entries.size() * 4 > (size_t)n_slots * 3) return KAS_ERR_UNSUPPORTED;   // too many nested cuts
+    if (entries.size() * 2 > (size_t)n_slots) return KAS_ERR_UNSUPPORTED;   // too many nested cuts
 
     uint32_t *t = static_cast<uint32_t *>(host_tbl);
     memset(t, 0, need);
@@ -367,27 +458,79 @@ int kas_prefix_table_build(const uint8_t *names, const uint32_t *name_off, uint3
     uint32_t *slots = masks + (size_t)rows * RWP;
     for (uint32_t L = 0; L < rows; ++L)
         for (uint32_t k = 0; k < RW; ++k) masks[(size_t)L * RWP + k] = word_mask((int)k, (int)L + 1);
+
+    // masked words, unfinished hash and meta of every entry
+    struct Packed { uint32_t m[(KAS_MAX_REC_BYTES + 3) / 4]; uint32_t h, nbytes, meta; };
+    std::vector<Packed> packed;
     uint64_t len_mask = 0;
     for (const auto &kv : entries) {
         const std::string &s = kv.first;
-        const uint32_t nbytes = (uint32_t)s.size();
+        Packed pk;
+        memset(&pk, 0, sizeof(pk));
+        pk.nbytes = (uint32_t)s.size();
         uint8_t buf[KAS_MAX_REC_BYTES + 8] = {0};
-        memcpy(buf, s.data(), nbytes);
-        uint32_t m[(KAS_MAX_REC_BYTES + 3) / 4];
-        uint32_t h = 0;
+        memcpy(buf, s.data(), pk.nbytes);
         for (uint32_t k = 0; k < RW; ++k) {
-            m[k] = (uint32_t)buf[4 * k] | ((uint32_t)buf[4 * k + 1] << 8) |
-                   ((uint32_t)buf[4 * k + 2] << 16) | ((uint32_t)buf[4 * k + 3] << 24);
-            h += m[k] * hash_word_constant((int)k);
+            pk.m[k] = (uint32_t)buf[4 * k] | ((uint32_t)buf[4 * k + 1] << 8) |
+                      ((uint32_t)buf[4 * k + 2] << 16) | ((uint32_t)buf[4 * k + 3] << 24);
+            pk.h += pk.m[k] * hash_word_constant((int)k);
         }
-        const uint32_t tag = hash_finish(h, nbytes);
-        uint32_t slot = hash_slot(tag, 32u - log2_slots);
-        while (slots[(size_t)slot * EW + RW] != 0u) slot = (slot + 1) & (n_slots - 1);
-        uint32_t *e = slots + (size_t)slot * EW;
-        for (uint32_t k = 0; k < RW; ++k) e[k] = m[k];
-        e[RW] = tag;
-        e[RW + 1] = kv.second.q | (kv.second.ext ? kExtFlag : 0u);
-        len_mask |= 1ull << (nbytes - 1);
+        pk.meta = kv.second.q | (kv.second.ext ? kExtFlag : 0u);
+        len_mask |= 1ull << (pk.nbytes - 1);
+        packed.push_back(pk);
+    }
+    const uint32_t slot_shift = 32u - log2_slots;
+    const size_t E = packed.size();
+    std::vector<int> owner(n_slots);
+    uint32_t seed = 0;
+    bool placed = false, two_slot = false;
+    // 1) a seed that puts every entry alone in its home slot
+    for (uint32_t trial = 0; trial < 20000 && !placed; ++trial) {
+        seed = trial * 0x9E3779B9u + 1u;
+        std::fill(owner.begin(), owner.end(), -1);
+        bool ok = true;
+        for (size_t i = 0; i < E && ok; ++i) {
+            const uint32_t a = hash_slot_a(hash_finish(packed[i].h, packed[i].nbytes, seed), slot_shift);
+            if (owner[a] >= 0) ok = false;
+            else owner[a] = (int)i;
+        }
+        placed = ok;
+    }
+    // 2) otherwise either of two slots (cuckoo insertion with bounded eviction walks)
+    for (uint32_t trial = 0; trial < 64 && !placed; ++trial) {
+        seed = trial * 0x7F4A7C15u + 0x51ED27u;
+        std::fill(owner.begin(), owner.end(), -1);
+        bool ok = true;
+        for (size_t i = 0; i < E && ok; ++i) {
+            int cur = (int)i;
+            uint32_t avoid = 0xFFFFFFFFu;
+            bool done = false;
+            for (int kick = 0; kick < 512 && !done; ++kick) {
+                const uint32_t tag = hash_finish(packed[cur].h, packed[cur].nbytes, seed);
+                const uint32_t a = hash_slot_a(tag, slot_shift), b = hash_slot_b(tag, slot_shift);
+                if (owner[a] < 0) { owner[a] = cur; done = true; }
+                else if (owner[b] < 0) { owner[b] = cur; done = true; }
+                else {
+                    const uint32_t victim_slot = (a == avoid) ? b : a;
+                    const int victim = owner[victim_slot];
+                    owner[victim_slot] = cur;
+                    cur = victim;
+                    avoid = victim_slot;
+                }
+            }
+            ok = done;
+        }
+        placed = ok;
+        two_slot = ok;
+    }
+    if (!placed) return KAS_ERR_UNSUPPORTED;
+    for (uint32_t sl = 0; sl < n_slots; ++sl) {
+        if (owner[sl] < 0) continue;
+        const Packed &pk = packed[owner[sl]];
+        uint32_t *e = slots + (size_t)sl * EW;
+        for (uint32_t k = 0; k < RW; ++k) e[k] = pk.m[k];
+        e[RW] = 0u;
+        e[RW + 1] = pk.meta;
     }
     t[0] = kTableMagic;
     t[1] = rec_bytes;
@@ -395,8 +538,8 @@ int kas_prefix_table_build(const uint8_t *names, const uint32_t *name_off, uint3
     t[3] = n_slots;
     t[4] = (uint32_t)len_mask;
     t[5] = (uint32_t)(len_mask >> 32);
-    t[6] = EW;
-    t[7] = log2_slots;
+    t[6] = seed;
+    t[7] = log2_slots | (two_slot ? 0x100u : 0u);
     return KAS_OK;
 }
 

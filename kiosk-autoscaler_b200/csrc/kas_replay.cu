@@ -88,7 +88,8 @@ __device__ __forceinline__ int32_t decide_simple(uint32_t tally, const PolDev &p
     if (!K1) {
         // floor(tally / kpp) = high 64 bits of magic * tally; the quotient fits 32 bits
         const uint32_t lo_hi = __umulhi((uint32_t)p.magic, tally);
-        q = (uint32_t)(((uint64_t)(uint32_t)(p.magic >> 32) * tally + lo_hi) >> 32);
+        const uint32_t mh = (uint32_t)(((uint64_t)(uint32_t)(p.magic >> 32) * tally + lo_hi) >> 32);
+        q = p.magic ? mh : tally;                  // magic == 0 encodes kpp == 1
     }
     int32_t d = (int32_t)min(q, 0x7FFFFFFFu);   // saturating keeps every comparison's outcome
     d = max(min(d, p.mx), p.mn);

@@ -14,16 +14,23 @@
 // has no continuation: nothing longer can match.  Nested queue names (a key
 // counts for "predict" and for "predict:zstack") fall out of the same walk.
 //
+// Lookups never loop.  The host searches for a hash seed under which every
+// entry sits alone in its home slot ("one-slot" tables: small name sets, the
+// usual case); when no such seed is found entries may sit in either of two
+// slots (cuckoo placement, "two-slot" tables).  A candidate is an entry iff its
+// masked words equal the words stored in (one of) its slot(s); an empty slot
+// holds zeros and a candidate always holds its ':'.
+//
 // Device image (uint32 words):
-//   [0] magic  [1] rec_bytes  [2] n_prefix  [3] n_slots (power of two)
+//   [0] magic  [1] rec_bytes  [2] n_prefix  [3] n_slots (power of two, >= 8)
 //   [4] len_mask_lo  [5] len_mask_hi   (bit L set <=> some entry has name length L)
-//   [6] entry_words EW  [7] log2(n_slots)
+//   [6] hash seed   [7] log2(n_slots) | two_slot << 8
 //   length masks: (rec_bytes-11) rows of RWP words; row L holds, for each region
 //       word, the mask of the bytes below L+1 (RWP = region words rounded up to 4)
 //   entries: n_slots rows of EW words: RW region words (masked, zero padded),
-//       tag (finalised hash | 1; 0 = empty slot), meta (queue id | ext << 31,
-//       queue id 0x7FFFFFFF = virtual).  EW = RW + 2 is a multiple of 4, so a row
-//       is read with 128-bit shared loads.
+//       one reserved word, meta (queue id | ext << 31, queue id 0x7FFFFFFE =
+//       virtual).  EW = RW + 2 is a multiple of 4, so a row is read with 128-bit
+//       shared loads.
 #pragma once
 #include <stdint.h>
 
@@ -35,10 +42,10 @@
 
 namespace kas {
 
-constexpr uint32_t kTableMagic = 0x4B415332u;  // "KAS2"
+constexpr uint32_t kTableMagic = 0x4B415333u;  // "KAS3"
 constexpr uint32_t kTableHeaderWords = 8;
 constexpr uint32_t kLiteralLen = 11;           // strlen("processing-")
-constexpr uint32_t kVirtualQueue = 0x7FFFFFFFu;
+constexpr uint32_t kVirtualQueue = 0x7FFFFFFEu;   // with the ext flag still != kNoQueue (the "not an entry" answer)
 constexpr uint32_t kExtFlag = 0x80000000u;
 
 KAS_HD constexpr uint32_t region_words(uint32_t rec_bytes) { return (rec_bytes - kLiteralLen + 3) / 4; }
@@ -55,14 +62,15 @@ KAS_HD uint32_t word_mask(int k, int nbytes) {
 // Hash of the masked region words: a multiply-add chain (IMAD on the device)
 // with one odd constant per word, then a finaliser.  `tag` is never 0.
 KAS_HD uint32_t hash_word_constant(int k) { return 0x9E3779B1u + 0x3C6EF372u * (uint32_t)k; }
-KAS_HD uint32_t hash_finish(uint32_t h, uint32_t nbytes) {
-    h += nbytes * 0x85EBCA6Bu;
+KAS_HD uint32_t hash_finish(uint32_t h, uint32_t nbytes, uint32_t seed) {
+    h += nbytes * 0x85EBCA6Bu + seed;
     h ^= h >> 15;
     h *= 0xC2B2AE35u;
     h ^= h >> 13;
-    return h | 1u;
+    return h;
 }
 // slot_shift = 32 - log2(n_slots); n_slots >= 8, so the shift is below 32
-KAS_HD uint32_t hash_slot(uint32_t tag, uint32_t slot_shift) { return (tag * 0x27D4EB2Fu) >> slot_shift; }
+KAS_HD uint32_t hash_slot_a(uint32_t tag, uint32_t slot_shift) { return (tag * 0x27D4EB2Fu) >> slot_shift; }
+KAS_HD uint32_t hash_slot_b(uint32_t tag, uint32_t slot_shift) { return (tag * 0x165667B1u + 0x9E3779B9u) >> slot_shift; }
 
 }  // namespace kas

@@ -38,9 +38,9 @@ def test_golden_tally_cases():
         keys = helpers.latin(case['keyspace'])
         W = engine.rec_bytes_for(names)
         heads = oracle.pack_heads(keys, W)
-        # queue names were written as latin-1 in the fixture keyspace
-        enc = [q.encode('latin-1') for q in names]
-        got = _gpu_counts(enc, heads, W) if len(keys) else [0] * len(names)
+        # names reach the server as UTF-8 (redis.py:159-161 of the reference); the fixture's
+        # keys are raw bytes, so a latin-1 'tr\xe9' inside a key is not the queue name 'tré'
+        got = _gpu_counts(names, heads, W) if len(keys) else [0] * len(names)
         want = [case['redis_keys'][q] - case['lists'].get(q, 0) for q in names]
         assert got == want, case['queues']
         ran += 1

@@ -1,0 +1,296 @@
+"""CPU-only checks: the C-ABI library loads and exports what include/kas.h
+declares, host-side ingest helpers, table builder validation, the drop-in
+package surface, scale.py configuration, the RedisClient wrapper and the
+Kubernetes-side methods (mirroring the reference's own tests)."""
+import ctypes
+import os
+import re
+import sys
+import types
+
+import numpy as np
+import pytest
+
+from tests import helpers
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    from autoscaler import engine
+    hdr = open(os.path.join(ROOT, 'include', 'kas.h')).read()
+    declared = set(re.findall(r'KAS_API\s+[\w\s\*]+?\b(kas_\w+)\s*\(', hdr))
+    assert len(declared) >= 16
+    L = engine.lib()
+    for name in declared:
+        assert hasattr(L, name), name
+    assert declared == set(engine.SYMBOLS), declared ^ set(engine.SYMBOLS)
+    assert L.kas_version() == 100
+    assert L.kas_strerror(-5) == b'integer division or modulo by zero'
+    assert L.kas_rec_bytes_for(7) == 32 and L.kas_rec_bytes_for(4) == 16 and L.kas_rec_bytes_for(21) == 48
+    # struct layouts the header promises
+    assert ctypes.sizeof(engine.Policy) == 12 and ctypes.sizeof(engine.Totals) == 16
+    assert engine.TOTALS_DTYPE.itemsize == 16
+
+
+def test_no_cuda_means_loud_failure():
+    import torch
+    from autoscaler import engine
+    if torch.cuda.is_available():
+        pytest.skip('CUDA present')
+    with pytest.raises(RuntimeError, match='no CPU fallback'):
+        engine.decide([1], [1], [0], [1], [0])
+    import autoscaler
+    s = autoscaler.Autoscaler(helpers.ListRedis(), 'q')
+    with pytest.raises(RuntimeError):
+        s.tally_queues()
+    with pytest.raises(RuntimeError):
+        s.get_desired_pods('q', 1, 0, 1, 0)
+
+
+def test_missing_library_is_an_import_error(monkeypatch):
+    from autoscaler import engine
+    monkeypatch.setattr(engine, '_lib', None)
+    monkeypatch.setattr(engine, 'LIB_PATH', '/nonexistent/libkas.so')
+    with pytest.raises(ImportError, match='no CPU fallback'):
+        engine.lib()
+
+
+def test_prefix_table_builder_validation():
+    from autoscaler import engine
+    t = engine.build_prefix_table(['predict', 'track'], 32).view(np.uint32)
+    assert t[1] == 32 and t[2] == 2 and t[4] == (1 << 7) | (1 << 5) and (t[7] >> 8) == 0
+    # nested names add cut entries: "a:" (virtual) for "a:b"
+    t = engine.build_prefix_table(['a:b', 'abc'], 32).view(np.uint32)
+    assert t[4] == (1 << 1) | (1 << 3)
+    with pytest.raises(engine.GlobQueueNameError):
+        engine.build_prefix_table(['tra?k'], 32)
+    for bad in (['a', 'a'], ['x' * 21], ['a\0b']):
+        with pytest.raises(engine.KasError):
+            engine.build_prefix_table(bad, 32)
+    with pytest.raises(ValueError):
+        engine.build_prefix_table([], 32)
+    # a big table falls back to two-slot placement and still builds
+    t = engine.build_prefix_table(['n%d' % i for i in range(1024)], 32).view(np.uint32)
+    assert (t[7] >> 8) == 1
+
+
+def test_pack_and_index_helpers_match_oracle():
+    from autoscaler import engine, snapshot
+    from oracle import oracle
+    keys = [b'processing-a:1', b'', b'x' * 100, b'processing-predict:zstack:host', b'\x00\xff\n'[:2]]
+    snap = snapshot.KeySnapshot.from_keys(keys)
+    for W in (16, 32, 48, 64):
+        assert (snap.heads(W) == oracle.pack_heads(keys, W)).all()
+    dump = b'\n'.join([b'k1', b'processing-q:abc', b'', b'last-without-newline'])
+    s2 = snapshot.KeySnapshot.from_dump(dump)
+    assert len(s2) == 4
+    assert (s2.heads(32) == oracle.pack_heads(dump.split(b'\n'), 32)).all()
+    s3 = snapshot.KeySnapshot.from_dump(dump + b'\n')
+    assert len(s3) == 4 and (s3.heads(16) == s2.heads(16)).all()
+    assert len(snapshot.KeySnapshot.from_dump(b'')) == 0
+    with pytest.raises(ValueError):
+        snapshot.KeySnapshot.from_heads(np.zeros((3, 16), np.uint8)).heads(32)
+
+
+def test_synthetic_keys_are_deterministic_and_sliceable():
+    from autoscaler import engine
+    names = helpers.c2_queue_names(64)
+    h1, b1, o1 = engine.synth_keys_host(7, 0, 5000, names, long_tail=True, rec_bytes=32, want_blob=True)
+    h2, _, _ = engine.synth_keys_host(7, 1000, 100, names, long_tail=True, rec_bytes=32)
+    assert (h1[1000:1100] == h2).all()
+    h3, _, _ = engine.synth_keys_host(7, 0, 5000, names, long_tail=True, rec_bytes=32, threads=1)
+    assert (h1 == h3).all()
+    lens = np.diff(o1.astype(np.int64))
+    assert lens.max() > 300 and (engine.pack_heads_host(b1, o1, 32) == h1).all()
+    starts = np.array([bytes(b1[o1[i]:o1[i] + 11]) == b'processing-' for i in range(2000)])
+    assert 0.55 < starts.mean() < 0.8
+
+
+def test_package_surface_and_init_parsing():
+    import autoscaler
+    assert autoscaler.Autoscaler and autoscaler.redis.RedisClient
+    for case in helpers.golden_json('known_answers')['init']:
+        s = autoscaler.Autoscaler(None, case['queues'], case['delim'])
+        assert list(s.redis_keys) == case['keys'] and set(s.redis_keys.values()) == {0}
+    s = autoscaler.Autoscaler('client')
+    assert s.redis_keys == {'predict': 0} and s.redis_client == 'client'
+    assert s.managed_resource_types == {'deployment', 'job'} and s.completed_statuses == {'done', 'failed'}
+    assert s.logger.name == 'Autoscaler'
+    assert 'llen' in autoscaler.redis.REDIS_READONLY_COMMANDS
+    assert 'scan_iter' not in autoscaler.redis.REDIS_READONLY_COMMANDS
+    assert len(autoscaler.redis.REDIS_READONLY_COMMANDS) == 83
+
+
+def _patch_kube(scaler, kube):
+    scaler.get_apps_v1_client = lambda: kube
+    scaler.get_batch_v1_client = lambda: kube
+
+
+def test_get_current_pods_like_reference_test():
+    # autoscaler_test.py:155-182
+    import autoscaler
+    scaler = autoscaler.Autoscaler(helpers.ListRedis(), 'queue')
+    _patch_kube(scaler, helpers.DummyKubernetes())
+    with pytest.raises(ValueError):
+        scaler.get_current_pods('namespace', 'bad_type', 'pod')
+    assert scaler.get_current_pods('ns', 'deployment', 'pod1') == 4
+    assert scaler.get_current_pods('ns', 'deployment', 'pod2') == 8
+    assert scaler.get_current_pods('ns', 'deployment', 'pod2', True) == 8
+    assert scaler.get_current_pods('ns', 'deployment', 'pod1', True) == 0
+    assert scaler.get_current_pods('ns', 'job', 'pod1') == 1
+    assert scaler.get_current_pods('ns', 'job', 'pod2') == 2
+    assert scaler.get_current_pods('ns', 'job', 'absent') == 0
+
+
+def test_scale_resource_like_reference_test():
+    # autoscaler_test.py:212-236
+    import autoscaler
+    scaler = autoscaler.Autoscaler(helpers.ListRedis(), 'queue')
+    _patch_kube(scaler, helpers.DummyKubernetes())
+    assert not scaler.scale_resource(1, 1, 'deployment', 'ns', 'name')
+    assert scaler.scale_resource(2, 1, 'job', 'ns', 'name')
+    assert scaler.scale_resource(2, 1, 'deployment', 'ns', 'name')
+    with pytest.raises(ValueError):
+        scaler.scale_resource(2, 1, 'badvalue', 'ns', 'name')
+
+
+def test_kube_wrappers_log_and_reraise_api_exception():
+    # autoscaler_test.py:104-153
+    import autoscaler
+
+    class Failing(helpers.DummyKubernetes):
+        def _boom(self, *a, **k):
+            raise helpers.ApiException('thrown on purpose')
+        list_namespaced_deployment = list_namespaced_job = _boom
+        patch_namespaced_deployment = patch_namespaced_job = _boom
+
+    scaler = autoscaler.Autoscaler(helpers.ListRedis(), 'queue')
+    _patch_kube(scaler, helpers.DummyKubernetes())
+    scaler.patch_namespaced_deployment('job', 'ns', {'spec': {'replicas': 1}})
+    scaler.patch_namespaced_job('job', 'ns', {'spec': {'parallelism': 1}})
+    assert len(scaler.list_namespaced_deployment('ns')) == 2
+    _patch_kube(scaler, Failing())
+    for call in (lambda: scaler.list_namespaced_deployment('ns'), lambda: scaler.list_namespaced_job('ns'),
+                 lambda: scaler.patch_namespaced_deployment('p', 'ns', {}),
+                 lambda: scaler.patch_namespaced_job('p', 'ns', {})):
+        with pytest.raises(helpers.ApiException):
+            call()
+
+
+# ---- RedisClient wrapper, driven like the reference's redis_test.py ---------
+def _fake_redis_module(fail_first=None):
+    mod = types.ModuleType('redis')
+    mod.exceptions = types.ModuleType('redis.exceptions')
+
+    class ConnectionError(Exception):  # noqa: A001
+        pass
+
+    class ResponseError(Exception):
+        pass
+
+    mod.exceptions.ConnectionError, mod.exceptions.ResponseError = ConnectionError, ResponseError
+    state = {'fail': fail_first, 'made': []}
+
+    class StrictRedis(object):
+        def __init__(self, host='h', port=1, **kw):
+            self.host, self.port, self.kw = host, port, kw
+            state['made'].append(self)
+
+        def sentinel_masters(self):
+            return {'mymaster': {'ip': 'master', 'port': 6379}}
+
+        def sentinel_slaves(self, name):
+            return [{'ip': 'slave%d' % i, 'port': 6379} for i in range(3)]
+
+        def llen(self, q):
+            if state['fail'] is not None:
+                err, state['fail'] = state['fail'], None
+                raise err
+            return 7 if self.host.startswith('slave') else -1
+
+        def lpush(self, q, v):
+            return 'master' if self.host == 'master' else 'WRONG'
+
+        def scan_iter(self, match=None, count=None):
+            return iter([self.host])
+
+        def boom(self):
+            raise ValueError('other error')
+
+    mod.StrictRedis = StrictRedis
+    return mod, state
+
+
+def test_redis_client_routing_and_retries(monkeypatch):
+    import autoscaler
+    mod, state = _fake_redis_module()
+    monkeypatch.setitem(sys.modules, 'redis', mod)
+    monkeypatch.setitem(sys.modules, 'redis.exceptions', mod.exceptions)
+    c = autoscaler.redis.RedisClient(host='sentinel', port=26379, backoff=0)
+    assert c._redis_master.host == 'master' and len(c._redis_slaves) == 3
+    assert state['made'][0].kw == {'decode_responses': True, 'charset': 'utf-8'}
+    assert c.llen('q') == 7                       # read-only -> a replica
+    assert c.lpush('q', 'x') == 'master'          # write -> master
+    assert list(c.scan_iter(match='processing-*', count=1000)) == ['master']   # not in the read-only set
+    state['fail'] = mod.exceptions.ConnectionError('down')
+    assert c.llen('q') == 7                       # retried
+    state['fail'] = mod.exceptions.ResponseError('BUSY Redis is busy. SCRIPT KILL')
+    assert c.llen('q') == 7                       # retried
+    state['fail'] = mod.exceptions.ResponseError('WRONGTYPE')
+    with pytest.raises(mod.exceptions.ResponseError):
+        c.llen('q')
+    with pytest.raises(ValueError):
+        c.boom()
+
+    # a plain server answers SENTINEL with a ResponseError: keep using it for everything
+    def no_sentinel(self):
+        raise mod.exceptions.ResponseError('unknown command')
+    monkeypatch.setattr(mod.StrictRedis, 'sentinel_masters', no_sentinel)
+    c2 = autoscaler.redis.RedisClient(host='plain', port=6379)
+    assert c2._redis_master is c2._sentinel and c2._redis_slaves == [c2._sentinel]
+
+
+def test_scale_py_config(monkeypatch):
+    import importlib.util
+    spec = importlib.util.spec_from_file_location(
+        'kas_scale', os.path.join(ROOT, 'kiosk-autoscaler_b200', 'scale.py'))
+    scale = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(scale)
+    for k in ('REDIS_HOST', 'REDIS_PORT', 'REDIS_INTERVAL', 'QUEUES', 'QUEUE_DELIMITER', 'INTERVAL',
+              'RESOURCE_NAMESPACE', 'RESOURCE_TYPE', 'RESOURCE_NAME', 'MIN_PODS', 'MAX_PODS', 'KEYS_PER_POD'):
+        monkeypatch.delenv(k, raising=False)
+    with pytest.raises(Exception):
+        scale.load_config()                       # RESOURCE_NAME has no default (scale.py:88)
+    monkeypatch.setenv('RESOURCE_NAME', 'consumer')
+    cfg = scale.load_config()
+    assert cfg == dict(redis_host='redis-master', redis_port=6379, redis_backoff=1,
+                       queues='predict,track', queue_delim=',', interval=5, namespace='default',
+                       resource_type='deployment', name='consumer', min_pods=0, max_pods=1,
+                       keys_per_pod=1)
+    monkeypatch.setenv('MAX_PODS', '12')
+    monkeypatch.setenv('QUEUES', 'a|b')
+    monkeypatch.setenv('QUEUE_DELIMITER', '|')
+    cfg = scale.load_config()
+    assert cfg['max_pods'] == 12 and cfg['queues'] == 'a|b' and cfg['queue_delim'] == '|'
+    monkeypatch.setenv('KEYS_PER_POD', 'x')
+    with pytest.raises(ValueError):
+        scale.load_config()
+
+
+def test_shard_ranges_cover_everything():
+    from autoscaler import replay
+    for n in (0, 1, 7, 100, 1_000_003):
+        for w in (1, 2, 3, 8):
+            for align in (1, 4):
+                parts = [replay.shard_range(n, r, w, align) for r in range(w)]
+                assert parts[0][0] == 0 and parts[-1][1] == n
+                assert all(a[1] == b[0] for a, b in zip(parts, parts[1:]))
+                assert all(lo % align == 0 for lo, _ in parts)
+    go = np.array([0, 2, 3, 7, 8, 12], dtype=np.uint64)
+    seen = []
+    for r in range(2):
+        r_lo, r_hi, q_lo, q_hi, local = replay.shard_groups(go, r, 2)
+        assert local[0] == 0 and local[-1] == q_hi - q_lo
+        seen.append((r_lo, r_hi, q_lo, q_hi))
+    assert seen[0][1] == seen[1][0] and seen[0][3] == seen[1][2] and seen[1][3] == 12
