@@ -50,8 +50,8 @@ typedef enum kas_status {
     KAS_ERR_ZERO_DIVISION = -5, /* keys_per_pod == 0 (reference: ZeroDivisionError,
                                    autoscaler.py:217)                           */
     KAS_ERR_GLOB_META = -6,     /* queue name holds * ? [ \ : a live glob in the
-                                   reference (autoscaler.py:69); use
-                                   kas_glob_count                                */
+                                   reference (autoscaler.py:69), which the
+                                   prefix kernel does not evaluate               */
     KAS_ERR_TOO_SMALL = -7      /* caller's output buffer is too small          */
 } kas_status;
 
@@ -101,7 +101,9 @@ KAS_API int kas_pack_heads(const uint8_t *d_blob, const uint64_t *d_off, uint64_
  * caller, staged in shared memory by the match kernel.
  * Names must be unique, free of NUL and of the glob metacharacters * ? [ \
  * (KAS_ERR_GLOB_META otherwise), at most rec_bytes-12 bytes long, and at most
- * KAS_MAX_PREFIXES of them.
+ * KAS_MAX_PREFIXES of them; the table (which also holds every cut of a name at
+ * an inner ':') must fit 200 KB of shared memory, else KAS_ERR_UNSUPPORTED /
+ * a size of 0.
  * ---------------------------------------------------------------------- */
 #define KAS_MAX_PREFIXES 1024u
 #define KAS_MAX_REC_BYTES 64u
