@@ -50,7 +50,12 @@ def lib():
 
 
 def max_threads():
-    return max(1, min(lib().kas_oracle_max_threads(), os.cpu_count() or 1))
+    """Every core this process may run on.  OMP_NUM_THREADS is deliberately not
+    consulted (torchrun sets it to 1): the CPU baseline is meant to use the host."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
 
 
 def _names_blob(queues):
