@@ -200,6 +200,39 @@ typedef struct kas_replay_args {
 KAS_API int kas_replay(const kas_replay_args *args, void *stream);
 
 /* ------------------------------------------------------------------------
+ * Patch-event stream of a replay: the calls Autoscaler.scale_resource would
+ * have made (autoscaler.py:221-242).  An event is a tick on which
+ * desired != current (:227); the body the reference sends is
+ * {'spec': {'replicas': to_pods}} for a deployment (:236) and
+ * {'spec': {'parallelism': to_pods}} for a job (:232) -- the resource type
+ * only picks the field name, so it stays on the host.
+ * Events are grouped by resource, in tick order inside a resource:
+ *     events of resource r = d_events[d_event_off[r] .. d_event_off[r+1])
+ * Same inputs, domain and policy handling as kas_replay (d_totals / d_sums /
+ * d_dense of args are ignored); one policy, args->policies[policy_index].
+ *
+ *   1. kas_patch_event_offsets  counts per resource and scans: writes
+ *      d_event_off[0..R]; d_event_off[R] is the number of events.  Needs
+ *      kas_patch_events_scratch_bytes(R) bytes of scratch (0 for R <= 4096).
+ *   2. kas_patch_event_emit     writes the events that fit in `capacity`
+ *      (every event whose index is below capacity; size the buffer from
+ *      d_event_off[R]).
+ * ---------------------------------------------------------------------- */
+typedef struct kas_patch_event {
+    uint32_t tick;      /* tick on which the patch would have been issued   */
+    int32_t from_pods;  /* current pods read at that tick (autoscaler.py:252) */
+    int32_t to_pods;    /* value patched                                      */
+} kas_patch_event;
+
+KAS_API size_t kas_patch_events_scratch_bytes(uint64_t n_resources);
+KAS_API int kas_patch_event_offsets(const kas_replay_args *args, uint32_t policy_index,
+                                    uint64_t *d_event_off /* [R+1] */, void *d_scratch,
+                                    size_t scratch_bytes, void *stream);
+KAS_API int kas_patch_event_emit(const kas_replay_args *args, uint32_t policy_index,
+                                 const uint64_t *d_event_off, kas_patch_event *d_events,
+                                 uint64_t capacity, void *stream);
+
+/* ------------------------------------------------------------------------
  * Synthetic workload generators (no counterpart in the reference, which has
  * no benchmark; used by bench.py and the tests; specified in DESIGN.md so the
  * oracle can rebuild any element independently).

@@ -56,6 +56,7 @@ class Totals(C.Structure):
     _fields_ = [('pod_ticks', C.c_int64), ('n_patches', C.c_uint32), ('final_current', C.c_int32)]
 
 
+EVENT_DTYPE = np.dtype([('tick', '<u4'), ('from_pods', '<i4'), ('to_pods', '<i4')])
 TOTALS_DTYPE = np.dtype([('pod_ticks', '<i8'), ('n_patches', '<u4'), ('final_current', '<i4')])
 
 
@@ -93,6 +94,11 @@ SYMBOLS = {
     'kas_decide': (C.c_int, [C.c_void_p] * 5 + [C.c_uint64, C.c_int, C.c_void_p, C.c_void_p,
                                                 C.c_void_p]),
     'kas_replay': (C.c_int, [C.POINTER(ReplayArgs), C.c_void_p]),
+    'kas_patch_events_scratch_bytes': (C.c_size_t, [C.c_uint64]),
+    'kas_patch_event_offsets': (C.c_int, [C.POINTER(ReplayArgs), C.c_uint32, C.c_void_p, C.c_void_p,
+                                          C.c_size_t, C.c_void_p]),
+    'kas_patch_event_emit': (C.c_int, [C.POINTER(ReplayArgs), C.c_uint32, C.c_void_p, C.c_void_p,
+                                       C.c_uint64, C.c_void_p]),
     'kas_synth_trace': (C.c_int, [C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint64, C.c_void_p,
                                   C.c_void_p]),
     'kas_synth_keys_host': (C.c_int, [C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p,
@@ -342,6 +348,33 @@ def replay(d_llen, n_ticks, n_queues, policies, d_inprog=None, inprog_mode=0, d_
     if want_dense:
         out['dense'] = dense
     return out
+
+
+def patch_events(d_llen, n_ticks, n_queues, policy, d_inprog=None, inprog_mode=0, d_group_off=None,
+                 n_resources=None, d_cur0=None):
+    """Patch-event stream of one policy.  Returns (event_off numpy uint64 [R+1],
+    events numpy structured [total] with tick/from_pods/to_pods)."""
+    torch = require_cuda()
+    k, a, b = (int(v) for v in policy)
+    for v in (k, a, b):
+        if not -(2 ** 31) <= v < 2 ** 31:
+            raise OverflowError('policy values must fit in int32, got %r' % (policy,))
+    R = n_queues if n_resources is None else n_resources
+    parr = (Policy * 1)(Policy(k, a, b))
+    dev = d_llen.device
+    args = ReplayArgs(ptr(d_llen), ptr(d_inprog), inprog_mode, n_ticks, n_queues, R,
+                      ptr(d_group_off), ptr(d_cur0), parr, 1, None, None, None)
+    off = torch.empty(R + 1, dtype=torch.int64, device=dev)
+    nscratch = lib().kas_patch_events_scratch_bytes(R)
+    scratch = torch.empty(max(nscratch, 8), dtype=torch.uint8, device=dev)
+    check(lib().kas_patch_event_offsets(C.byref(args), 0, ptr(off), ptr(scratch), nscratch,
+                                        stream_ptr()), 'kas_patch_event_offsets')
+    total = int(off[R].item())
+    events = torch.empty((max(total, 1), 12), dtype=torch.uint8, device=dev)
+    check(lib().kas_patch_event_emit(C.byref(args), 0, ptr(off), ptr(events), total, stream_ptr()),
+          'kas_patch_event_emit')
+    ev = events.cpu().numpy().reshape(-1)[:total * 12].view(EVENT_DTYPE)
+    return off.cpu().numpy().view(np.uint64), ev
 
 
 def totals_to_host(d_totals):

@@ -110,6 +110,54 @@ def replay_fleet(llen, policies, inprog=None, group_off=None, cur0=None, want_to
     return res
 
 
+class PatchLog(object):
+    """The patch calls of a replay, per resource (CSR) and in tick order:
+    ``events[off[r]:off[r+1]]`` with fields tick / from_pods / to_pods."""
+
+    def __init__(self, off, events, resource_types):
+        self.off, self.events, self.resource_types = off, events, resource_types
+
+    def __len__(self):
+        return int(self.off[-1])
+
+    def of(self, r):
+        return self.events[int(self.off[r]):int(self.off[r + 1])]
+
+    def bodies(self, r):
+        """(tick, body) pairs as scale_resource would have sent them
+        (autoscaler.py:232 for a job, :236 for a deployment)."""
+        rt = self.resource_types if isinstance(self.resource_types, str) else self.resource_types[r]
+        field = RESOURCE_FIELD[rt]
+        return [(int(e['tick']), {'spec': {field: int(e['to_pods'])}}) for e in self.of(r)]
+
+
+def patch_events(llen, policy, inprog=None, group_off=None, cur0=None, resource_types='deployment'):
+    """Patch-event stream of ONE policy over a fleet (same inputs as replay_fleet).
+    ``resource_types`` is one type for all resources or a sequence with one
+    entry per resource ('deployment' / 'job'); it only selects the body field."""
+    types = [resource_types] if isinstance(resource_types, str) else list(resource_types)
+    for rt in types:
+        _check_type(rt)
+    torch = engine.require_cuda()
+    d_llen = _to_device_i32(llen, torch, 'llen')
+    T, Q = int(d_llen.shape[0]), int(d_llen.shape[1])
+    d_ip = _to_device_i32(inprog, torch, 'inprog')
+    mode = 0 if d_ip is None else (1 if d_ip.dim() == 1 else 2)
+    d_go, R = None, Q
+    if group_off is not None:
+        go = np.ascontiguousarray(group_off, dtype=np.uint64)
+        if go[0] != 0 or go[-1] != Q or (np.diff(go.astype(np.int64)) < 0).any():
+            raise ValueError('group_off must rise from 0 to Q')
+        R = len(go) - 1
+        d_go = torch.from_numpy(go.view(np.int64)).to('cuda')
+    if not isinstance(resource_types, str) and len(types) != R:
+        raise ValueError('resource_types must have one entry per resource')
+    d_c0 = _to_device_i32(cur0, torch, 'cur0')
+    off, ev = engine.patch_events(d_llen, T, Q, policy, d_inprog=d_ip, inprog_mode=mode,
+                                  d_group_off=d_go, n_resources=R, d_cur0=d_c0)
+    return PatchLog(off, ev, resource_types)
+
+
 def replay_one(queue_names, llen_trace, policies, inprog=None, current_pods=0,
                resource_type='deployment', managed=('deployment', 'job'), want_dense=False):
     """One resource fed by ``len(queue_names)`` queues (what one reference pod

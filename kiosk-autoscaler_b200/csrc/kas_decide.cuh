@@ -1,0 +1,101 @@
+// kas_decide.cuh -- the replica decision (autoscaler.py:197-219) as device code,
+// shared by the replay and the patch-event kernels.
+#pragma once
+#include "kas_common.cuh"
+
+namespace kas {
+
+struct PolDev {
+    uint64_t magic;  // ceil(2^64 / |kpp|); 0 when |kpp| == 1
+    int32_t mn, mx;
+    int32_t neg;     // -1 when kpp < 0, else 0
+    int32_t pad;
+};
+
+// Execution modes, chosen per launch by the host from the policies alone:
+//   kGeneric  any kpp != 0, any min/max: exact 64-bit path.
+//   kSimple   every policy has kpp >= 1 and min <= max (every sane configuration):
+//             a non-negative tally needs only a 32-bit multiply-high, the if/elif
+//             clamp is max(min(d, max), min), "never scale down to a non-zero count"
+//             is d > 0 ? max(d, cur) : d, and for a single-queue resource clipping
+//             the one-term sum again (autoscaler.py:259) changes nothing.
+//   kSimpleK1 kSimple with every kpp == 1 (scale.py:92 default): no division at all.
+// Negative trace values take the exact path in every mode; all modes give the
+// reference's integers.
+enum ReplayMode { kGeneric = 0, kSimple = 1, kSimpleK1 = 2 };
+
+// Host side: the device form of one policy (keys_per_pod != 0).
+static inline PolDev make_poldev(const kas_policy &p) {
+    PolDev d = {0, 0, 0, 0, 0};
+    const uint64_t ak = p.keys_per_pod < 0 ? (uint64_t)(-(int64_t)p.keys_per_pod) : (uint64_t)p.keys_per_pod;
+    d.magic = ak == 1 ? 0ull : (~0ull / ak) + 1ull;   // ceil(2^64/ak) (exact when ak | 2^64 too)
+    d.mn = p.min_pods;
+    d.mx = p.max_pods;
+    d.neg = p.keys_per_pod < 0 ? -1 : 0;
+    return d;
+}
+
+// Execution mode for a set of policies (see kas_replay.cu); -1 when a keys_per_pod is 0.
+static inline int replay_mode_for(const kas_policy *p, uint32_t n);
+
+#ifdef __CUDACC__
+// clip_pod_count (autoscaler.py:197-213), 32-bit form.  if/elif order kept.
+__device__ __forceinline__ int32_t clip32(int32_t d, int32_t mn, int32_t mx, int32_t cur) {
+    d = d > mx ? mx : (d < mn ? mn : d);
+    return (d > 0 && d < cur) ? cur : d;
+}
+// Same with a 64-bit candidate (a sum of per-queue decisions, or a quotient).
+__device__ __forceinline__ int32_t clip64(int64_t d, int32_t mn, int32_t mx, int32_t cur) {
+    int32_t r = d > (int64_t)mx ? mx : (d < (int64_t)mn ? mn : (int32_t)d);
+    return (r > 0 && r < cur) ? cur : r;
+}
+
+// tally // kpp with Python floor semantics for |tally| <= 2^32, any kpp != 0.
+__device__ __forceinline__ int64_t floordiv_any(int64_t tally, const PolDev &p) {
+    const int64_t t2 = (tally ^ (int64_t)p.neg) - (int64_t)p.neg;  // negate when kpp < 0
+    const int64_t s = t2 >> 63;
+    const uint64_t u = (uint64_t)(t2 ^ s);                          // floor(t/d) = ~((~t)/d), t < 0
+    const uint64_t q = p.magic ? __umul64hi(p.magic, u) : u;
+    return (int64_t)q ^ s;
+}
+
+// get_desired_pods (autoscaler.py:215-219) for one queue, exact for any input.
+__device__ __forceinline__ int32_t decide_exact(int32_t llen, int32_t inprog, const PolDev &p, int32_t cur) {
+    return clip64(floordiv_any((int64_t)llen + (int64_t)inprog, p), p.mn, p.mx, cur);
+}
+
+// The same for kpp >= 1, min <= max and a tally in [0, 2^32).
+template <bool K1>
+__device__ __forceinline__ int32_t decide_simple(uint32_t tally, const PolDev &p, int32_t cur) {
+    uint32_t q = tally;
+    if (!K1) {
+        // floor(tally / kpp) = high 64 bits of magic * tally; the quotient fits 32 bits
+        const uint32_t lo_hi = __umulhi((uint32_t)p.magic, tally);
+        const uint32_t mh = (uint32_t)(((uint64_t)(uint32_t)(p.magic >> 32) * tally + lo_hi) >> 32);
+        q = p.magic ? mh : tally;                  // magic == 0 encodes kpp == 1
+    }
+    int32_t d = (int32_t)min(q, 0x7FFFFFFFu);   // saturating keeps every comparison's outcome
+    d = max(min(d, p.mx), p.mn);
+    return d > 0 ? max(d, cur) : d;
+}
+
+template <int MODE>
+__device__ __forceinline__ int32_t decide(int32_t llen, int32_t inprog, const PolDev &p, int32_t cur) {
+    if (MODE != kGeneric && ((llen | inprog) >= 0))
+        return decide_simple<MODE == kSimpleK1>((uint32_t)llen + (uint32_t)inprog, p, cur);
+    return decide_exact(llen, inprog, p, cur);
+}
+
+#endif  // __CUDACC__
+
+static inline int replay_mode_for(const kas_policy *p, uint32_t n) {
+    int mode = 2;  // kSimpleK1
+    for (uint32_t s = 0; s < n; ++s) {
+        if (p[s].keys_per_pod == 0) return -1;
+        if (p[s].keys_per_pod < 0 || p[s].min_pods > p[s].max_pods) mode = 0;          // kGeneric
+        else if (p[s].keys_per_pod != 1 && mode == 2) mode = 1;                        // kSimple
+    }
+    return mode;
+}
+
+}  // namespace kas

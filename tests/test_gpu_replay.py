@@ -118,6 +118,17 @@ def test_large_replay_sampled_queues():
         assert tot['final_current'][q].tolist() == want['final'][0].tolist()
     assert (sums[:, 0] == tot['pod_ticks'].sum(0)).all()
     assert (sums[:, 1] == tot['n_patches'].astype(np.int64).sum(0)).all()
+    # patch-event stream at this size (245 scan tiles): offsets agree with the replay's own
+    # patch counts, sampled logs with the oracle
+    off, ev = engine.patch_events(trace, T, Q, pol[1])
+    assert (np.diff(off.astype(np.int64)) == tot['n_patches'][:, 1].astype(np.int64)).all()
+    assert len(ev) == int(sums[1, 1])
+    for q in rng.integers(0, Q, size=8).tolist():
+        col = coracle.trace_fill(seed, T, q, 1)
+        dense = coracle.replay(col, None, None, None, [pol[1]], want_dense=True)['dense'][0, :, 0]
+        mine = ev[int(off[q]):int(off[q + 1])]
+        assert [(int(e['tick']), int(e['from_pods']), int(e['to_pods'])) for e in mine] == \
+            _oracle_events(dense, 0)
     # sharding by resource: two halves generated independently give the same box-wide sums
     half = Q // 2
     acc = torch.zeros_like(out['sums'])
@@ -125,3 +136,61 @@ def test_large_replay_sampled_queues():
         part = engine.synth_trace(seed, T, lo, half)
         acc += engine.replay(part, T, half, pol, want_totals=False)['sums']
     assert (acc.cpu().numpy() == sums).all()
+
+
+def _oracle_events(dense_sr, cur0):
+    """(tick, from, to) of one resource from its dense trajectory."""
+    out, prev = [], int(cur0)
+    for t, v in enumerate(dense_sr.tolist()):
+        if v != prev:
+            out.append((t, prev, v))
+        prev = v
+    return out
+
+
+@pytest.mark.parametrize('shape', ['identity_small', 'identity_big', 'grouped'])
+def test_patch_event_stream(shape):
+    """f1: the calls scale_resource would have made, per resource in tick order."""
+    import autoscaler
+    from oracle import coracle
+    rng = np.random.default_rng({'identity_small': 1, 'identity_big': 2, 'grouped': 3}[shape])
+    T, Q = {'identity_small': (80, 700), 'identity_big': (25, 20_011), 'grouped': (60, 9000)}[shape]
+    llen, go = helpers.random_fleet(rng, T, Q, grouped=(shape == 'grouped'), neg=(shape == 'grouped'))
+    R = Q if go is None else len(go) - 1
+    cur0 = rng.integers(0, 9, size=R).astype(np.int32)
+    inprog = rng.integers(0, 3, size=Q).astype(np.int32)
+    types = [('job' if i % 3 == 0 else 'deployment') for i in range(R)]
+    for pol in [(1, 0, 1), (3, 1, 9), (-2, 0, 6), (2, 7, 4)]:
+        want = coracle.replay(llen, inprog, go, cur0, [pol], want_dense=True)
+        log = autoscaler.replay.patch_events(llen, pol, inprog=inprog, group_off=go, cur0=cur0,
+                                             resource_types=types)
+        assert len(log) == int(want['n_patches'].sum())
+        assert (np.diff(log.off.astype(np.int64)) == want['n_patches'][:, 0]).all()
+        for r in list(range(0, R, max(1, R // 50))) + [R - 1]:
+            ev = log.of(r)
+            assert [(int(e['tick']), int(e['from_pods']), int(e['to_pods'])) for e in ev] == \
+                _oracle_events(want['dense'][0, :, r], cur0[r])
+        field = 'parallelism' if types[0] == 'job' else 'replicas'
+        assert all(set(b['spec']) == {field} for _, b in log.bodies(0))
+    with pytest.raises(ZeroDivisionError):
+        autoscaler.replay.patch_events(llen, (0, 0, 1))
+    with pytest.raises(ValueError):
+        autoscaler.replay.patch_events(llen, (1, 0, 1), resource_types='badvalue')
+
+
+def test_patch_events_match_reference_fixture():
+    """The patches the reference issued in tests/golden/scale_cases.json."""
+    import autoscaler
+    from oracle import oracle
+    for case in helpers.golden_json('scale_cases'):
+        names = list(oracle.parse_queues(case['queues'], case['delim']))
+        split = case['queues'].split(case['delim'])
+        llen = np.array([[dict(zip(split, row)).get(q, 0) for q in names] for row in case['depths']],
+                        dtype=np.int32)
+        inprog = np.array(oracle.match_counts(names, helpers.latin(case['keyspace'])), dtype=np.int32)
+        log = autoscaler.replay.patch_events(llen, (case['kpp'], case['min'], case['max']), inprog=inprog,
+                                             group_off=np.array([0, len(names)], dtype=np.uint64),
+                                             cur0=np.array([case['cur0']], dtype=np.int32),
+                                             resource_types=case['type'])
+        field = 'replicas' if case['type'] == 'deployment' else 'parallelism'
+        assert [b['spec'][field] for _, b in log.bodies(0)] == case['patches']
