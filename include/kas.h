@@ -52,7 +52,9 @@ typedef enum kas_status {
     KAS_ERR_GLOB_META = -6,     /* queue name holds * ? [ \ : a live glob in the
                                    reference (autoscaler.py:69), which the
                                    prefix kernel does not evaluate               */
-    KAS_ERR_TOO_SMALL = -7      /* caller's output buffer is too small          */
+    KAS_ERR_TOO_SMALL = -7,     /* caller's output buffer is too small          */
+    KAS_ERR_STATIC_LIMIT = -8   /* more resources than the library's built-in
+                                   scratch covers (kas_patch_event_offsets_static) */
 } kas_status;
 
 KAS_API int kas_version(void);
@@ -231,6 +233,39 @@ KAS_API int kas_patch_event_offsets(const kas_replay_args *args, uint32_t policy
 KAS_API int kas_patch_event_emit(const kas_replay_args *args, uint32_t policy_index,
                                  const uint64_t *d_event_off, kas_patch_event *d_events,
                                  uint64_t capacity, void *stream);
+
+/* kas_patch_event_offsets without a scratch buffer from the caller.
+ * (No counterpart in the reference, which never touches a GPU.)
+ *
+ * Who needs it: a caller that is not allowed to obtain device memory at the
+ * moment it wants the offsets.  Examples are a scaling service that sized all
+ * of its HBM at start-up (the trace alone is 80 GB per GPU at the 16M-queue
+ * configuration) and runs with a fixed budget afterwards, a plug-in inside a
+ * host process whose memory pool belongs to another framework, or a control
+ * loop that cannot afford the device-wide synchronisation a cudaMalloc /
+ * cudaFree pair brings.  For them the tile sums of the scan live in a fixed
+ * 64 KB array inside the library image instead: every GPU that loads libkas
+ * holds that array until the process exits.
+ *
+ * Same result as kas_patch_event_offsets, bit for bit; the caller still passes
+ * the trace and d_event_off[R+1].  The call makes no cudaMalloc / cudaFree and
+ * uses no allocating library routine.
+ *
+ * Limits and rules
+ *   - at most KAS_STATIC_SCRATCH_MAX_RESOURCES resources; beyond that the call
+ *     is refused with KAS_ERR_STATIC_LIMIT and nothing is launched (use
+ *     kas_patch_event_offsets with your own scratch).
+ *   - the first call on each device looks the array's device address up
+ *     (cudaGetSymbolAddress, with that device current) and remembers it; make
+ *     that first call before starting any stream capture.
+ *   - all calls on a device share the one array, which keeps whatever the
+ *     last call left in it.  Nothing has to be cleared -- each call writes every
+ *     tile sum before it reads it -- but two calls whose GPU work overlaps
+ *     (different streams, or different host threads on the same device) race
+ *     on it: keep them on one stream or order them yourself. */
+#define KAS_STATIC_SCRATCH_MAX_RESOURCES 33554432ull /* 8192 scan tiles of 4096 */
+KAS_API int kas_patch_event_offsets_static(const kas_replay_args *args, uint32_t policy_index,
+                                           uint64_t *d_event_off /* [R+1] */, void *stream);
 
 /* ------------------------------------------------------------------------
  * Synthetic workload generators (no counterpart in the reference, which has

@@ -22,6 +22,8 @@ KAS_ERR_ALIGNMENT = -4
 KAS_ERR_ZERO_DIVISION = -5
 KAS_ERR_GLOB_META = -6
 KAS_ERR_TOO_SMALL = -7
+KAS_ERR_STATIC_LIMIT = -8
+STATIC_SCRATCH_MAX_RESOURCES = 33554432
 
 MAX_PREFIXES = 1024
 MAX_REC_BYTES = 64
@@ -97,6 +99,8 @@ SYMBOLS = {
     'kas_patch_events_scratch_bytes': (C.c_size_t, [C.c_uint64]),
     'kas_patch_event_offsets': (C.c_int, [C.POINTER(ReplayArgs), C.c_uint32, C.c_void_p, C.c_void_p,
                                           C.c_size_t, C.c_void_p]),
+    'kas_patch_event_offsets_static': (C.c_int, [C.POINTER(ReplayArgs), C.c_uint32, C.c_void_p,
+                                                 C.c_void_p]),
     'kas_patch_event_emit': (C.c_int, [C.POINTER(ReplayArgs), C.c_uint32, C.c_void_p, C.c_void_p,
                                        C.c_uint64, C.c_void_p]),
     'kas_synth_trace': (C.c_int, [C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint64, C.c_void_p,

@@ -14,6 +14,8 @@
 #include "kas_common.cuh"
 #include "kas_decide.cuh"
 
+#include <mutex>
+
 namespace kas {
 
 constexpr int kEventThreads = 128;
@@ -235,6 +237,36 @@ int patch_event_offsets_impl(const kas_replay_args *args, uint32_t policy_index,
     return scan_counts_in_place(P.event_off + 1, P.R, d_tile_sums, stream);
 }
 
+// ---- built-in scratch for callers that must not allocate --------------------
+// The scan's tile sums, as a fixed array inside the library image: every GPU that
+// loads libkas holds these 64 KB until the process exits.  In host code the name
+// below is only a handle for cudaGetSymbolAddress, never a pointer to pass to a
+// kernel; the device address is looked up once per device and remembered.
+constexpr uint64_t kStaticTiles = KAS_STATIC_SCRATCH_MAX_RESOURCES / kScanTile;
+static_assert(KAS_STATIC_SCRATCH_MAX_RESOURCES % kScanTile == 0, "limit must be a whole number of scan tiles");
+static __device__ __align__(256) unsigned long long g_static_tile_sums[kStaticTiles];
+
+constexpr int kMaxDevices = 64;
+static std::mutex g_static_mu;
+static unsigned long long *g_static_addr[kMaxDevices] = {nullptr};
+
+// Device address of the built-in scratch on the CURRENT device.  The first call on
+// a device asks the runtime for it (no allocation: the array came with the module).
+static int static_tile_sums(unsigned long long **out) {
+    int dev = -1;
+    KAS_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return KAS_ERR_UNSUPPORTED;
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (g_static_addr[dev] == nullptr) {
+        void *p = nullptr;
+        KAS_CUDA_TRY(cudaGetSymbolAddress(&p, g_static_tile_sums));
+        if (p == nullptr) return KAS_ERR_CUDA;
+        g_static_addr[dev] = static_cast<unsigned long long *>(p);
+    }
+    *out = g_static_addr[dev];
+    return KAS_OK;
+}
+
 }  // namespace kas
 
 using namespace kas;
@@ -270,6 +302,21 @@ int kas_patch_event_emit(const kas_replay_args *args, uint32_t policy_index, con
     P.capacity = capacity;
     if (capacity == 0) return KAS_OK;
     return launch_events<true>(P, mode, static_cast<cudaStream_t>(stream));
+}
+
+int kas_patch_event_offsets_static(const kas_replay_args *args, uint32_t policy_index,
+                                   uint64_t *d_event_off, void *stream) {
+    if (!args || !d_event_off) return KAS_ERR_INVALID;
+    if (!aligned(d_event_off, 8)) return KAS_ERR_ALIGNMENT;
+    if (args->n_resources > KAS_STATIC_SCRATCH_MAX_RESOURCES) return KAS_ERR_STATIC_LIMIT;
+    unsigned long long *tile_sums = nullptr;
+    const int st = static_tile_sums(&tile_sums);
+    if (st != KAS_OK) return st;
+    // Nothing in the array has to start at zero: every tile sum the scan reads in this
+    // call is written by this call first (scan_tile_sums_kernel), whatever an earlier
+    // call left behind.
+    return patch_event_offsets_impl(args, policy_index, d_event_off, tile_sums,
+                                    static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

@@ -137,6 +137,9 @@ const char *kas_strerror(int status) {
         case KAS_ERR_ZERO_DIVISION: return "integer division or modulo by zero";
         case KAS_ERR_GLOB_META: return "queue name contains a glob metacharacter";
         case KAS_ERR_TOO_SMALL: return "output buffer too small";
+        case KAS_ERR_STATIC_LIMIT:
+            return "more resources than the built-in scratch covers (limit 33554432); "
+                   "use the variant that takes a scratch buffer";
     }
     return "unknown status";
 }
