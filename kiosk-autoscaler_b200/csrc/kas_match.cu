@@ -35,6 +35,17 @@ constexpr int kMatchThreads = 256;
 constexpr uint32_t kNoQueue = 0xFFFFFFFFu;
 constexpr size_t kMaxMatchSmem = 200 * 1024;
 
+// ':' detector, cheap form: 0x80 in every byte of w that equals 0x3A, and possibly
+// in bytes ABOVE such a byte of the same word (borrow).  The lowest flag of a word
+// is always a real colon, which is all the first step of a walk needs; the subtract
+// is written as a multiply-add so that it can issue on the FMA pipe (the integer ALU
+// pipe is this kernel's limiter).
+__device__ __forceinline__ uint32_t colon_flags_lowest_exact(uint32_t w) {
+    const uint32_t v = w ^ 0x3A3A3A3Au;
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, 1, 0xFEFEFEFF;" : "=r"(d) : "r"(v));   // v - 0x01010101
+    return d & ~v & 0x80808080u;
+}
 // ':' detector: 0x80 in every byte of w that equals 0x3A (exact, no carries).
 __device__ __forceinline__ uint32_t colon_flags(uint32_t w) {
     const uint32_t v = w ^ 0x3A3A3A3Au;
@@ -48,14 +59,14 @@ __device__ __forceinline__ uint32_t flags_to_top_nibble(uint32_t f) { return f *
 template <int NCHUNK>
 struct MatchCfg {
     static constexpr int kRecWords = 4 * NCHUNK;
-    static constexpr int kRW = (16 * NCHUNK - (int)kLiteralLen + 3) / 4;   // region words
+    static constexpr int kRW = (16 * NCHUNK - (int)kRegionStart) / 4;       // region words = record words 2..
     static constexpr int kRWP = (kRW + 3) / 4 * 4;                         // padded to 128-bit rows
     static constexpr int kEW = kRW + 2;                                    // entry words
-    static constexpr int kRows = 16 * NCHUNK - (int)kLiteralLen;           // name lengths 0..W-12
+    static constexpr int kRows = 16 * NCHUNK - (int)kRegionStart;           // colon positions inside the region
     static constexpr int kKeysPerThread = NCHUNK <= 2 ? KAS_MATCH_U : 2;
-    using mask_t = typename std::conditional<(kRows <= 32), uint32_t, uint64_t>::type;   // one bit per name length
-    // a deferred walk: region words + the colons still to visit, padded to 128-bit rows
-    static constexpr int kItemWords = (kRW + (int)(sizeof(mask_t) / 4) + 3) / 4 * 4;
+    using mask_t = typename std::conditional<(kRows <= 32), uint32_t, uint64_t>::type;   // one bit per colon position
+    // a deferred walk: region words + the position already dealt with, padded to 128-bit rows
+    static constexpr int kItemWords = (kRW + 1 + 3) / 4 * 4;
     static_assert(kEW % 4 == 0, "entry rows must be 128-bit multiples");
 };
 constexpr int kQueueItems = 64;   // per warp: at most 31 waiting + 32 pushed by one step
@@ -83,29 +94,39 @@ struct Matcher {
     mask_t len_mask;
     uint32_t waiting;   // deferred walks in this warp's queue (warp-uniform)
 
-    // Region words (bytes 11.. of the record) and the ':' positions that can end an
-    // entry.  Returns false when the record does not start with "processing-".
-    __device__ __forceinline__ bool prepare(const uint32_t (&x)[XW], uint32_t (&r)[RW], mask_t &colons) const {
-        // "processing-" = 70 72 6f 63 | 65 73 73 69 | 6e 67 2d
-        const bool literal = (x[0] == 0x636F7270u) & (x[1] == 0x69737365u) &
-                             ((x[2] & 0x00FFFFFFu) == 0x002D676Eu);
-#pragma unroll
-        for (int k = 0; k < RW; ++k)
-            r[k] = (3 + k < XW) ? __byte_perm(x[2 + k], x[3 + k], 0x6543) : (x[2 + k] >> 24);
-        colons = 0;   // bit L <=> region byte L is ':'
+    // bit P of the result <=> region byte P is ':' and some entry ends there.  EXACT =
+    // false uses the cheap detector, whose lowest set bit per word is still exact.
+    template <bool EXACT>
+    __device__ __forceinline__ mask_t colon_mask(const uint32_t (&r)[RW]) const {
+        mask_t colons = 0;
         if constexpr (sizeof(mask_t) == 4) {
 #pragma unroll
             for (int k = RW - 1; k >= 0; --k)
-                colons = __funnelshift_l(flags_to_top_nibble(colon_flags(r[k])), colons, 4);
+                colons = __funnelshift_l(
+                    flags_to_top_nibble(EXACT ? colon_flags(r[k]) : colon_flags_lowest_exact(r[k])), colons, 4);
         } else {
 #pragma unroll
             for (int k = RW - 1; k >= 0; --k)
-                colons = (colons << 4) | (mask_t)(flags_to_top_nibble(colon_flags(r[k])) >> 28);
+                colons = (colons << 4) |
+                         (mask_t)(flags_to_top_nibble(EXACT ? colon_flags(r[k]) : colon_flags_lowest_exact(r[k])) >> 28);
         }
-        // Only positions that are the length of some entry can match.  Dropping the
-        // others up front is safe because the table is closed under cutting at inner
-        // colons: a candidate that spans a colon at a non-entry length is no entry.
-        colons &= len_mask;
+        // Only positions where some entry ends can match.  Dropping the others up front
+        // is safe because the table is closed under cutting at inner colons: a candidate
+        // that spans a colon at a non-entry position is no entry.
+        return colons & len_mask;
+    }
+
+    // Region words (record words 2.., i.e. "ng-" + name + ...) and the ':' positions
+    // that can end an entry.  Returns false when the record does not start with
+    // "processi"; the remaining "ng-" is part of every stored string.
+    __device__ __forceinline__ bool prepare(const uint32_t (&x)[XW], uint32_t (&r)[RW], mask_t &colons) const {
+        // "processi" = 70 72 6f 63 | 65 73 73 69
+        const bool literal = (x[0] == 0x636F7270u) & (x[1] == 0x69737365u);
+#pragma unroll
+        for (int k = 0; k < RW; ++k) r[k] = x[2 + k];
+        // cheap detector: the FIRST set bit is exact (a spurious bit can only sit above a
+        // real colon of the same word); walks that go on recompute the exact mask
+        colons = colon_mask<false>(r);
         return literal;
     }
 
@@ -147,9 +168,10 @@ struct Matcher {
 
     // Nested queue names ("predict" and "predict:zstack") make a key's walk go on
     // past its first colon.  Few lanes need that, so instead of looping in place
-    // with most of the warp idle, they park the walk in the warp's queue; the warp
-    // resumes 32 parked walks at a time with every lane busy.
-    __device__ __forceinline__ void park(bool more, const uint32_t (&r)[RW], mask_t rest) {
+    // with most of the warp idle, they park the walk (region words + the position
+    // already dealt with) in the warp's queue; the warp resumes 32 parked walks at
+    // a time with every lane busy.
+    __device__ __forceinline__ void park(bool more, const uint32_t (&r)[RW], int done_upto) {
         const uint32_t who = __ballot_sync(0xFFFFFFFFu, more);
         if (who == 0u) return;
         if (more) {
@@ -159,8 +181,7 @@ struct Matcher {
             for (int k = 0; k < IW; ++k) v[k] = 0u;
 #pragma unroll
             for (int k = 0; k < RW; ++k) v[k] = r[k];
-            v[RW] = (uint32_t)rest;
-            if constexpr (sizeof(mask_t) == 8) v[RW + 1] = (uint32_t)((uint64_t)rest >> 32);
+            v[RW] = (uint32_t)done_upto;
 #pragma unroll
             for (int j = 0; j < IW / 4; ++j)
                 reinterpret_cast<uint4 *>(it)[j] = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
@@ -175,7 +196,7 @@ struct Matcher {
         const bool mine = lane < n;
         waiting -= n;
         uint32_t r[RW];
-        mask_t rest = 0;
+        int done_upto = 0;
         if (mine) {
             const uint32_t *it = sm.queue + (waiting + lane) * IW;
             uint32_t v[IW];
@@ -186,16 +207,18 @@ struct Matcher {
             }
 #pragma unroll
             for (int k = 0; k < RW; ++k) r[k] = v[k];
-            rest = (mask_t)v[RW];
-            if constexpr (sizeof(mask_t) == 8) rest |= (mask_t)((uint64_t)v[RW + 1] << 32);
+            done_upto = (int)v[RW];
         } else {
 #pragma unroll
             for (int k = 0; k < RW; ++k) r[k] = 0u;
         }
         __syncwarp();   // every lane has read its item before anyone parks on top of it
+        // the exact colon mask, minus what the walk has already dealt with
+        mask_t rest = colon_mask<true>(r) & ~((((mask_t)2) << done_upto) - (mask_t)1);
         bool more = false;
-        if (mine) {
-            const int L = first_bit<mask_t>(rest);
+        int L = 0;
+        if (mine && rest != 0) {
+            L = first_bit<mask_t>(rest);
             rest &= rest - 1;
             const uint32_t meta = lookup(r, L);
             if (meta != kNoQueue) {
@@ -204,7 +227,7 @@ struct Matcher {
                 more = (meta & kExtFlag) && rest != 0;
             }
         }
-        park(more, r, rest);
+        park(more, r, L);
     }
 
     // One record: its first colon is looked up here; the id of the queue it counts
@@ -215,17 +238,18 @@ struct Matcher {
         const bool literal = prepare(x, r, colons);
         uint32_t q = kNoQueue;
         bool more = false;
+        int L = 0;
         if (literal && colons != 0) {
-            const int L = first_bit<mask_t>(colons);
+            L = first_bit<mask_t>(colons);
             colons &= colons - 1;
             const uint32_t meta = lookup(r, L);
             if (meta != kNoQueue) {
                 const uint32_t id = meta & ~kExtFlag;
                 if (id != kVirtualQueue) q = id;
-                more = (meta & kExtFlag) && colons != 0;
+                more = (meta & kExtFlag) && colons != 0;   // may over-report: resume() re-checks exactly
             }
         }
-        park(more, r, colons);
+        park(more, r, L);
         while (waiting >= 32u) resume();
         return q;
     }
@@ -332,8 +356,7 @@ static size_t image_words(uint32_t n_prefix, uint32_t rec_bytes) {
 }
 
 static uint32_t item_words(uint32_t rec_bytes) {
-    const uint32_t mask_words = length_rows(rec_bytes) <= 32 ? 1 : 2;
-    return (region_words(rec_bytes) + mask_words + 3) / 4 * 4;
+    return (region_words(rec_bytes) + 1 + 3) / 4 * 4;
 }
 
 static size_t match_smem_bytes(uint32_t n_prefix, uint32_t rec_bytes) {
@@ -436,7 +459,8 @@ int kas_prefix_table_build(const uint8_t *names, const uint32_t *name_off, uint3
             if (c == '*' || c == '?' || c == '[' || c == '\\') return KAS_ERR_GLOB_META;
             if (c == 0) return KAS_ERR_UNSUPPORTED;
         }
-        std::string s(reinterpret_cast<const char *>(nm), len);
+        std::string s("ng-");                                               // kRegionLiteral bytes
+        s.append(reinterpret_cast<const char *>(nm), len);
         s.push_back(':');
         auto it = entries.find(s);
         if (it != entries.end() && it->second.q != kVirtualQueue) return KAS_ERR_INVALID;  // duplicate name
@@ -444,7 +468,8 @@ int kas_prefix_table_build(const uint8_t *names, const uint32_t *name_off, uint3
         else it->second.q = q;
         for (uint32_t i = 0; i < len; ++i) {
             if (nm[i] != ':') continue;
-            std::string cut(reinterpret_cast<const char *>(nm), i + 1);   // includes the inner colon
+            std::string cut("ng-");
+            cut.append(reinterpret_cast<const char *>(nm), i + 1);        // includes the inner colon
             auto jt = entries.find(cut);
             if (jt == entries.end()) entries[cut] = Entry{kVirtualQueue, true};
             else jt->second.ext = true;

@@ -59,10 +59,10 @@ def test_missing_library_is_an_import_error(monkeypatch):
 def test_prefix_table_builder_validation():
     from autoscaler import engine
     t = engine.build_prefix_table(['predict', 'track'], 32).view(np.uint32)
-    assert t[1] == 32 and t[2] == 2 and t[4] == (1 << 7) | (1 << 5) and (t[7] >> 8) == 0
+    assert t[1] == 32 and t[2] == 2 and t[4] == (1 << 10) | (1 << 8) and (t[7] >> 8) == 0
     # nested names add cut entries: "a:" (virtual) for "a:b"
     t = engine.build_prefix_table(['a:b', 'abc'], 32).view(np.uint32)
-    assert t[4] == (1 << 1) | (1 << 3)
+    assert t[4] == (1 << 4) | (1 << 6)   # colon positions count the "ng-" of the literal
     with pytest.raises(engine.GlobQueueNameError):
         engine.build_prefix_table(['tra?k'], 32)
     for bad in (['a', 'a'], ['x' * 21], ['a\0b']):
