@@ -51,7 +51,7 @@ typedef enum kas_status {
                                    autoscaler.py:217)                           */
     KAS_ERR_GLOB_META = -6,     /* queue name holds * ? [ \ : a live glob in the
                                    reference (autoscaler.py:69), which the
-                                   prefix kernel does not evaluate               */
+                                   prefix table cannot hold: use kas_glob_count  */
     KAS_ERR_TOO_SMALL = -7,     /* caller's output buffer is too small          */
     KAS_ERR_STATIC_LIMIT = -8   /* more resources than the library's built-in
                                    scratch covers (kas_patch_event_offsets_static) */
@@ -134,6 +134,23 @@ KAS_API int kas_match_count(const void *d_heads, uint64_t n_keys, uint32_t rec_b
 KAS_API int kas_match_count_accumulate(const void *d_heads, uint64_t n_keys, uint32_t rec_bytes,
                                const void *d_prefix_tbl, uint32_t n_prefix, uint64_t *d_counts,
                                void *stream);
+
+/* ------------------------------------------------------------------------
+ * General glob match and count, for queue names that hold * ? [ \ .
+ * autoscaler.py:69 formats the queue name into the SCAN pattern unescaped, so
+ * such a name is a live glob in the reference; this call counts, for each
+ * pattern, the keys it matches with the semantics of `SCAN ... MATCH`
+ * (autoscaler.py:70-71).  Patterns are whole globs, e.g. "processing-pre*:*".
+ * Keys are a blob + offsets in HBM (key i = blob[off[i] .. off[i+1]-sep_bytes)),
+ * because a glob may need all bytes of a key.  d_patterns holds the pattern
+ * bytes back to back, pattern q = [d_pat_off[q], d_pat_off[q+1]); pattern_bytes
+ * = d_pat_off[n_patterns] (at most 16 KB, at most KAS_MAX_PREFIXES patterns).
+ * d_counts: uint64 [n_patterns], overwritten.
+ * ---------------------------------------------------------------------- */
+KAS_API int kas_glob_count(const uint8_t *d_blob, const uint64_t *d_off, uint64_t n_keys,
+                           uint32_t sep_bytes, const uint8_t *d_patterns, const uint32_t *d_pat_off,
+                           uint32_t n_patterns, uint32_t pattern_bytes, uint64_t *d_counts,
+                           void *stream);
 
 /* ------------------------------------------------------------------------
  * Element-wise decision, the scalar API's arithmetic.

@@ -93,6 +93,8 @@ SYMBOLS = {
                                   C.c_void_p, C.c_void_p]),
     'kas_match_count_accumulate': (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p,
                                              C.c_uint32, C.c_void_p, C.c_void_p]),
+    'kas_glob_count': (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p,
+                                 C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]),
     'kas_decide': (C.c_int, [C.c_void_p] * 5 + [C.c_uint64, C.c_int, C.c_void_p, C.c_void_p,
                                                 C.c_void_p]),
     'kas_replay': (C.c_int, [C.POINTER(ReplayArgs), C.c_void_p]),
@@ -291,6 +293,23 @@ def match_count(d_heads, n_keys, rec_bytes, d_table, n_prefix, d_counts=None, ac
     check(fn(ptr(d_heads), n_keys, rec_bytes, ptr(d_table), n_prefix, ptr(d_counts), stream_ptr()),
           'kas_match_count')
     return d_counts
+
+
+def glob_count(d_blob, d_off, n_keys, patterns, sep_bytes=0):
+    """General glob match and count on a device-resident blob+offsets keyspace.
+    patterns: sequence of bytes globs.  Returns an int64-typed CUDA tensor."""
+    torch = require_cuda()
+    pats = [bytes(p) for p in patterns]
+    poff = np.zeros(len(pats) + 1, dtype=np.uint32)
+    poff[1:] = np.cumsum([len(p) for p in pats])
+    pblob = np.frombuffer(b''.join(pats) + b'\0', dtype=np.uint8).copy()
+    dev = d_off.device
+    d_pat = torch.from_numpy(pblob).to(dev)
+    d_poff = torch.from_numpy(poff.view(np.int32)).to(dev)
+    counts = torch.empty(len(pats), dtype=torch.int64, device=dev)
+    check(lib().kas_glob_count(ptr(d_blob), ptr(d_off), n_keys, sep_bytes, ptr(d_pat), ptr(d_poff),
+                               len(pats), int(poff[-1]), ptr(counts), stream_ptr()), 'kas_glob_count')
+    return counts
 
 
 def counts_to_host(d_counts):

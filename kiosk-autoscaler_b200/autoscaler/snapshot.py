@@ -78,6 +78,18 @@ class KeySnapshot(object):
                                                             sep_bytes=self.sep_bytes)
         return self._heads[rec_bytes]
 
+    def device_blob(self, device='cuda'):
+        """(blob, offsets) resident in HBM, for the glob kernel."""
+        torch = engine.require_cuda()
+        key = ('blob', str(device))
+        if key not in self._device:
+            blob = np.ascontiguousarray(self.blob)
+            if blob.size == 0:
+                blob = np.zeros(1, dtype=np.uint8)
+            self._device[key] = (torch.from_numpy(blob.copy()).to(device),
+                                 torch.from_numpy(self.off.view(np.int64).copy()).to(device))
+        return self._device[key]
+
     def device_heads(self, rec_bytes, device='cuda'):
         """Heads resident in HBM (cached per width)."""
         torch = engine.require_cuda()
@@ -90,13 +102,35 @@ class KeySnapshot(object):
         return self._device[key]
 
 
+def _is_glob(q):
+    return any(ch in engine.GLOB_META for ch in engine.encode_name(q))
+
+
 def tally_snapshot(snapshot, queue_names, device='cuda'):
     """SCAN-count term for every queue over one snapshot: list of int, in the
-    order of ``queue_names`` (autoscaler.py:69-71 of the reference)."""
+    order of ``queue_names`` (autoscaler.py:69-71 of the reference).  Literal
+    names go through the prefix kernel in one pass; names holding glob
+    metacharacters -- live globs in the reference -- through the glob kernel."""
     names = list(queue_names)
-    for q in names:
-        if any(ch in engine.GLOB_META for ch in engine.encode_name(q)):
-            engine.check(engine.KAS_ERR_GLOB_META, 'tally of queue %r' % (q,))
+    out = [0] * len(names)
+    plain = [i for i, q in enumerate(names) if not _is_glob(q)]
+    globs = [i for i, q in enumerate(names) if _is_glob(q)]
+    if plain:
+        for i, c in zip(plain, _tally_prefixes(snapshot, [names[i] for i in plain], device)):
+            out[i] = c
+    if globs:
+        if snapshot.off is None:
+            raise ValueError('queue names with glob metacharacters need the whole keys; this '
+                             'snapshot only holds fixed-width heads')
+        d_blob, d_off = snapshot.device_blob(device)
+        pats = [b'processing-' + bytes(engine.encode_name(names[i])) + b':*' for i in globs]
+        counts = engine.glob_count(d_blob, d_off, len(snapshot), pats, sep_bytes=snapshot.sep_bytes)
+        for i, c in zip(globs, engine.counts_to_host(counts)):
+            out[i] = int(c)
+    return out
+
+
+def _tally_prefixes(snapshot, names, device):
     torch = engine.require_cuda()
     rec_bytes = engine.rec_bytes_for(names)
     if rec_bytes > engine.MAX_REC_BYTES:

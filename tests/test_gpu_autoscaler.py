@@ -40,8 +40,10 @@ def test_tally_queues_live_client_single_scan():
     want = oracle.tally_queues({q: 0 for q in scaler.redis_keys}, client.llen, keys)
     assert scaler.redis_keys == want
     assert client.scans == ['processing-*']          # one scan for all queues
-    with pytest.raises(NotImplementedError):
-        autoscaler.Autoscaler(client, queues='pre*').tally_queues()
+    # a queue name with glob metacharacters is a live glob in the reference (autoscaler.py:69)
+    g = autoscaler.Autoscaler(client, queues='pre*,tra?k,track')
+    g.tally_queues()
+    assert g.redis_keys == oracle.tally_queues({q: 0 for q in g.redis_keys}, client.llen, keys)
 
 
 def test_scale_with_stateful_cluster_matches_fixtures():
