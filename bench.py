@@ -285,35 +285,13 @@ def run_ours(args):
 
     # ---- end to end: host heads -> H2D -> K1 -> counts on the host -----------------
     e2e_steps = max(2, min(args.steps, 4))
-    chunk_keys = 8_388_608
-    copy_stream = torch.cuda.Stream(device=dev)
-    stage = [torch.empty(chunk_keys * W, dtype=torch.uint8, device=dev) for _ in range(2)]
-    free_ev = [torch.cuda.Event() for _ in range(2)]
-    out_host = torch.empty(N_PREFIX, dtype=torch.int64).pin_memory()
+    from autoscaler import snapshot as ksnap
+    streamer = ksnap.StreamingTally(names, chunk_keys=8_388_608, device=dev)
+    out_host = streamer.host_counts
 
     def e2e_step():
-        main = torch.cuda.current_stream()
-        d_counts.zero_()
-        for b in range(2):
-            free_ev[b].record(main)
-        i = 0
-        for lo in range(0, n, chunk_keys):
-            hi = min(n, lo + chunk_keys)
-            b = i & 1
-            with torch.cuda.stream(copy_stream):
-                copy_stream.wait_event(free_ev[b])
-                stage[b][:(hi - lo) * W].copy_(host_heads[lo * W:hi * W], non_blocking=True)
-                ready = torch.cuda.Event()
-                ready.record(copy_stream)
-            main.wait_event(ready)
-            engine.match_count(stage[b], hi - lo, W, table, N_PREFIX, d_counts=d_counts,
-                               accumulate=True)
-            free_ev[b].record(main)
-            i += 1
-        if world > 1:
-            dist.all_reduce(d_counts)
-        out_host.copy_(d_counts, non_blocking=True)
-        return i
+        # the public end-to-end call: pinned host heads -> H2D -> K1 -> counts on the host
+        streamer.enqueue(host_heads, n, reduce=(dist.all_reduce if world > 1 else None))
 
     e2e_step()
     torch.cuda.synchronize()
@@ -322,9 +300,8 @@ def run_ours(args):
     w0 = time.perf_counter()
     g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     g0.record()
-    launches_e2e = 0
     for _ in range(e2e_steps):
-        launches_e2e += e2e_step()
+        e2e_step()
     g1.record()
     torch.cuda.synchronize()
     e2e_ms = g0.elapsed_time(g1) / e2e_steps
@@ -339,9 +316,9 @@ def run_ours(args):
     e2e = {'value': world * n / (e2e_ms * 1e-3), 'unit': 'keys/s', 'h2d_bytes_per_step': n * W,
            'd2h_bytes_per_step': 8 * N_PREFIX, 'ms_per_step': e2e_ms, 'steps': e2e_steps,
            'matches_resident_result': e2e_ok,
-           'path': 'pinned host heads -> chunked double-buffered H2D -> kas_match_count_accumulate '
-                   '-> counts D2H'}
-    del stage
+           'path': 'autoscaler.snapshot.StreamingTally: pinned host heads -> chunked double-buffered '
+                   'H2D -> kas_match_count_accumulate -> counts D2H'}
+    del streamer
 
     # ---- replay (K2), BASELINE config 3 per GPU -------------------------------------
     rep = None

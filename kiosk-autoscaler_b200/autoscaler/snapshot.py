@@ -142,6 +142,72 @@ def _tally_prefixes(snapshot, names, device):
     return [int(c) for c in engine.counts_to_host(counts)]
 
 
+class StreamingTally(object):
+    """Tally a snapshot whose packed heads sit in (pinned) host memory: the heads
+    are copied to the GPU in chunks on a copy stream into two staging buffers
+    while the match kernel consumes the previous chunk, and only the uint64
+    counts come back.  This is the end-to-end form of ``tally_queues``'s SCAN
+    term for snapshots that are not resident in HBM (or larger than it)."""
+
+    def __init__(self, queue_names, chunk_keys=8 << 20, device='cuda'):
+        torch = engine.require_cuda()
+        self.names = list(queue_names)
+        for q in self.names:
+            if _is_glob(q):
+                engine.check(engine.KAS_ERR_GLOB_META, 'streaming tally of queue %r' % (q,))
+        self.rec_bytes = engine.rec_bytes_for(self.names)
+        self.device = torch.device(device)
+        self.chunk_keys = int(chunk_keys)
+        self.table = torch.from_numpy(engine.build_prefix_table(self.names, self.rec_bytes)).to(self.device)
+        self.stage = [torch.empty(self.chunk_keys * self.rec_bytes, dtype=torch.uint8, device=self.device)
+                      for _ in range(2)]
+        self.free = [torch.cuda.Event() for _ in range(2)]
+        self.copy_stream = torch.cuda.Stream(device=self.device)
+        self.counts = torch.empty(len(self.names), dtype=torch.int64, device=self.device)
+        self.host_counts = torch.empty(len(self.names), dtype=torch.int64).pin_memory()
+        self.launches = 0
+
+    def enqueue(self, host_heads, n_keys, reduce=None):
+        """Queue the whole pipeline on the current stream (no host sync).
+        ``host_heads``: uint8 tensor of n_keys*rec_bytes bytes, ideally pinned.
+        ``reduce``: optional callable applied to the device counts before the copy
+        back (the box-wide all-reduce).  Returns the pinned host tensor the counts
+        land in once the stream has drained."""
+        torch = engine.require_cuda()
+        W = self.rec_bytes
+        flat = host_heads.reshape(-1)
+        main = torch.cuda.current_stream(self.device)
+        self.counts.zero_()
+        for b in range(2):
+            self.free[b].record(main)
+        i = 0
+        for lo in range(0, n_keys, self.chunk_keys):
+            hi = min(n_keys, lo + self.chunk_keys)
+            b = i & 1
+            with torch.cuda.stream(self.copy_stream):
+                self.copy_stream.wait_event(self.free[b])
+                self.stage[b][:(hi - lo) * W].copy_(flat[lo * W:hi * W], non_blocking=True)
+                ready = torch.cuda.Event()
+                ready.record(self.copy_stream)
+            main.wait_event(ready)
+            engine.match_count(self.stage[b], hi - lo, W, self.table, len(self.names),
+                               d_counts=self.counts, accumulate=True)
+            self.free[b].record(main)
+            i += 1
+        self.launches += i
+        if reduce is not None:
+            reduce(self.counts)
+        self.host_counts.copy_(self.counts, non_blocking=True)
+        return self.host_counts
+
+    def run(self, host_heads, n_keys, reduce=None):
+        """enqueue() + wait; returns the counts as a list of int."""
+        torch = engine.require_cuda()
+        out = self.enqueue(host_heads, n_keys, reduce)
+        torch.cuda.current_stream(self.device).synchronize()
+        return [int(v) for v in out.numpy().view(np.uint64)]
+
+
 class SnapshotRedis(object):
     """A Redis stand-in over a key snapshot: what the offline replay feeds the
     unchanged ``Autoscaler``.  ``llen`` answers from ``lists``;

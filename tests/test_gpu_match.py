@@ -136,3 +136,36 @@ def test_full_size_properties():
     total = engine.counts_to_host(engine.match_count(d_heads, n, W, tbl, 64)).astype(np.int64)
     assert (total == np.sum(per_chunk, axis=0)).all()
     assert 0.45 * n < total.sum() < 0.75 * n
+
+
+def test_device_pack_and_streaming_tally():
+    """Ingest: the device packer equals the host packer / oracle, and the streaming
+    (host-resident heads, chunked H2D) tally equals the resident one."""
+    import torch
+    from autoscaler import engine, snapshot
+    from oracle import coracle, oracle
+    names = helpers.c2_queue_names(40)
+    n = 300_007
+    heads, blob, off = engine.synth_keys_host(9, 0, n, names, long_tail=True, rec_bytes=32, want_blob=True)
+    d_blob = torch.from_numpy(blob).cuda()
+    d_off = torch.from_numpy(off.view(np.int64)).cuda()
+    for W in (16, 32, 48, 64):
+        dev = engine.pack_heads_device(d_blob, d_off, n, W).cpu().numpy()
+        host = engine.pack_heads_host(blob, off, W)
+        assert (dev == host).all()
+        if W == 32:
+            assert (host == heads).all()
+            keys = [bytes(blob[off[i]:off[i + 1]]) for i in range(2000)]
+            assert (host[:2000] == oracle.pack_heads(keys, W)).all()
+    # newline dump, separator excluded, on the device packer too
+    dump = b'\n'.join(bytes(blob[off[i]:off[i + 1]]) for i in range(5000)) + b'\n'
+    s2 = snapshot.KeySnapshot.from_dump(dump)
+    dd = engine.pack_heads_device(torch.from_numpy(np.frombuffer(dump, np.uint8).copy()).cuda(),
+                                  torch.from_numpy(s2.off.view(np.int64)).cuda(), len(s2), 32, sep_bytes=1)
+    assert (dd.cpu().numpy() == heads[:5000]).all()
+    want = coracle.match_counts(names, blob, off).tolist()
+    st = snapshot.StreamingTally(names, chunk_keys=65_536)
+    pinned = torch.from_numpy(heads).pin_memory()
+    assert st.run(pinned, n) == want
+    assert st.run(pinned, n) == want            # reusable
+    assert st.run(pinned, 1) == coracle.match_counts(names, blob[:off[1]], off[:2]).tolist()
