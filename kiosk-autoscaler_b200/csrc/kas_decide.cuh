@@ -9,12 +9,12 @@ struct PolDev {
     uint64_t magic;  // ceil(2^64 / |kpp|); 0 when |kpp| == 1
     int32_t mn, mx;
     int32_t neg;     // -1 when kpp < 0, else 0
-    int32_t pad;
+    uint32_t k1;     // 1 when |kpp| == 1 (then magic == 0), else 0
 };
 
 // Execution modes, chosen per launch by the host from the policies alone:
 //   kGeneric  any kpp != 0, any min/max: exact 64-bit path.
-//   kSimple   every policy has kpp >= 1 and min <= max (every sane configuration):
+//   kSimple   every policy has kpp >= 1 and min <= max and max >= 0 (every sane configuration):
 //             a non-negative tally needs only a 32-bit multiply-high, the if/elif
 //             clamp is max(min(d, max), min), "never scale down to a non-zero count"
 //             is d > 0 ? max(d, cur) : d, and for a single-queue resource clipping
@@ -32,6 +32,7 @@ static inline PolDev make_poldev(const kas_policy &p) {
     d.mn = p.min_pods;
     d.mx = p.max_pods;
     d.neg = p.keys_per_pod < 0 ? -1 : 0;
+    d.k1 = ak == 1 ? 1u : 0u;
     return d;
 }
 
@@ -64,18 +65,20 @@ __device__ __forceinline__ int32_t decide_exact(int32_t llen, int32_t inprog, co
     return clip64(floordiv_any((int64_t)llen + (int64_t)inprog, p), p.mn, p.mx, cur);
 }
 
-// The same for kpp >= 1, min <= max and a tally in [0, 2^32).
+// The same for kpp >= 1, min <= max, max >= 0 and a tally in [0, 2^32).
 template <bool K1>
 __device__ __forceinline__ int32_t decide_simple(uint32_t tally, const PolDev &p, int32_t cur) {
     uint32_t q = tally;
     if (!K1) {
-        // floor(tally / kpp) = high 64 bits of magic * tally; the quotient fits 32 bits
+        // floor(tally / kpp) = high 64 bits of magic * tally (the quotient fits 32 bits);
+        // kpp == 1 has magic == 0 and k1 == 1, so the same multiply-adds give q = tally
         const uint32_t lo_hi = __umulhi((uint32_t)p.magic, tally);
         const uint32_t mh = (uint32_t)(((uint64_t)(uint32_t)(p.magic >> 32) * tally + lo_hi) >> 32);
-        q = p.magic ? mh : tally;                  // magic == 0 encodes kpp == 1
+        q = tally * p.k1 + mh;
     }
-    int32_t d = (int32_t)min(q, 0x7FFFFFFFu);   // saturating keeps every comparison's outcome
-    d = max(min(d, p.mx), p.mn);
+    // if/elif clamp with 0 <= max and min <= max: the unsigned min already lands in
+    // [0, max], so no saturation of q is needed before the signed max with min
+    const int32_t d = max((int32_t)min(q, (uint32_t)p.mx), p.mn);
     return d > 0 ? max(d, cur) : d;
 }
 
@@ -92,7 +95,7 @@ static inline int replay_mode_for(const kas_policy *p, uint32_t n) {
     int mode = 2;  // kSimpleK1
     for (uint32_t s = 0; s < n; ++s) {
         if (p[s].keys_per_pod == 0) return -1;
-        if (p[s].keys_per_pod < 0 || p[s].min_pods > p[s].max_pods) mode = 0;          // kGeneric
+        if (p[s].keys_per_pod < 0 || p[s].min_pods > p[s].max_pods || p[s].max_pods < 0) mode = 0;   // kGeneric
         else if (p[s].keys_per_pod != 1 && mode == 2) mode = 1;                        // kSimple
     }
     return mode;

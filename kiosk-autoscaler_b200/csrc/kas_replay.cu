@@ -48,8 +48,17 @@ __device__ __forceinline__ long long warp_sum_ll(long long v) {
 // IPMODE 0: no in-progress term, 1: one value per queue, 2: one per (tick, queue).
 // Blocks are numbered policy-chunk fastest, so the chunks that read the same
 // trace columns run together and share them through L2.
+#ifndef KAS_REPLAY_SWEEP_SP
+#define KAS_REPLAY_SWEEP_SP 2     // policies per thread under a sweep
+#endif
+#ifndef KAS_REPLAY_MINB_S1
+#define KAS_REPLAY_MINB_S1 6      // resident blocks per SM (register budget), one policy per thread
+#endif
+#ifndef KAS_REPLAY_MINB_SWEEP
+#define KAS_REPLAY_MINB_SWEEP 4   // the same with several policies per thread
+#endif
 template <int VEC, int SP, int IPMODE, int MODE>
-__global__ void __launch_bounds__(kReplayThreads)
+__global__ void __launch_bounds__(kReplayThreads, (SP == 1 ? KAS_REPLAY_MINB_S1 : KAS_REPLAY_MINB_SWEEP))
 replay_identity_kernel(const __grid_constant__ ReplayParams P) {
     constexpr int U = kTickUnroll;
     const uint32_t ny = (P.pol_count + SP - 1) / SP;
@@ -422,7 +431,7 @@ int kas_replay(const kas_replay_args *a, void *stream_v) {
                           ? a->n_policies - first : (uint32_t)kMaxPoliciesPerLaunch;
         P.inprog_mode = a->inprog_mode;
         for (uint32_t s = 0; s < (uint32_t)kMaxPoliciesPerLaunch; ++s) {
-            PolDev d = {0, 0, 0, 0, 0};
+            PolDev d = {0, 0, 0, 0, 0u};
             if (s < P.pol_count) d = make_poldev(a->policies[first + s]);
             P.pol[s] = d;
         }
@@ -431,7 +440,7 @@ int kas_replay(const kas_replay_args *a, void *stream_v) {
                 if (vec4) launch_identity<4, 1>(P, mode, stream);
                 else launch_identity<1, 1>(P, mode, stream);
             } else {
-                if (vec4) launch_identity<4, 4>(P, mode, stream);
+                if (vec4) launch_identity<4, KAS_REPLAY_SWEEP_SP>(P, mode, stream);
                 else launch_identity<1, 4>(P, mode, stream);
             }
         } else {

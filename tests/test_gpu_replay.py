@@ -51,7 +51,9 @@ def test_c1_reference_run():
 POLICY_SETS = {
     'one': [(1, 0, 1)],
     'sweep': [(k, a, b) for k in (1, 2, 5, 10, 50) for a in (0, 1) for b in (1, 4, 16, 64)],
-    'quirks': [(3, 9, 5), (1, -2, 3), (2 ** 31 - 1, 0, 7), (1, 0, 2 ** 31 - 1), (7, 0, 0)],
+    'quirks': [(3, 9, 5), (1, -2, 3), (2 ** 31 - 1, 0, 7), (1, 0, 2 ** 31 - 1), (7, 0, 0), (2, -5, -1)],
+    'negmax': [(1, -4, -2), (3, -(2 ** 31), -1)],
+    'edge': [(1, 0, 2 ** 31 - 1), (2, 0, 2 ** 31 - 1), (1, 2 ** 31 - 1, 2 ** 31 - 1), (3, -7, 0)],
     'negative': [(-1, 0, 5), (-3, -4, 6), (-(2 ** 31), 0, 3), (2, 0, 4)],
 }
 
