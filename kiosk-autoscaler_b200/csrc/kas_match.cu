@@ -37,13 +37,13 @@ constexpr size_t kMaxMatchSmem = 200 * 1024;
 
 // ':' detector, cheap form: 0x80 in every byte of w that equals 0x3A, and possibly
 // in bytes ABOVE such a byte of the same word (borrow).  The lowest flag of a word
-// is always a real colon, which is all the first step of a walk needs; the subtract
-// is written as a multiply-add so that it can issue on the FMA pipe (the integer ALU
-// pipe is this kernel's limiter).
-__device__ __forceinline__ uint32_t colon_flags_lowest_exact(uint32_t w) {
+// is always a real colon, which is all the first step of a walk needs.  The integer
+// ALU pipe is this kernel's limiter and the FMA pipe is nearly idle, so the subtract
+// is issued there as v * one - 0x01010101 with `one` a kernel argument equal to 1
+// (a literal 1 would be folded back into an ALU add).
+__device__ __forceinline__ uint32_t colon_flags_lowest_exact(uint32_t w, uint32_t one) {
     const uint32_t v = w ^ 0x3A3A3A3Au;
-    uint32_t d;
-    asm("mad.lo.u32 %0, %1, 1, 0xFEFEFEFF;" : "=r"(d) : "r"(v));   // v - 0x01010101
+    const uint32_t d = v * one + 0xFEFEFEFFu;
     return d & ~v & 0x80808080u;
 }
 // ':' detector: 0x80 in every byte of w that equals 0x3A (exact, no carries).
@@ -89,7 +89,7 @@ struct Matcher {
     static constexpr int XW = Cfg::kRecWords, RW = Cfg::kRW, RWP = Cfg::kRWP, EW = Cfg::kEW,
                          IW = Cfg::kItemWords;
     MatchSmem sm;
-    uint32_t seed, slot_shift, lane, lanemask_lt;
+    uint32_t seed, slot_shift, lane, lanemask_lt, one;
     bool two_slot;
     mask_t len_mask;
     uint32_t waiting;   // deferred walks in this warp's queue (warp-uniform)
@@ -103,12 +103,12 @@ struct Matcher {
 #pragma unroll
             for (int k = RW - 1; k >= 0; --k)
                 colons = __funnelshift_l(
-                    flags_to_top_nibble(EXACT ? colon_flags(r[k]) : colon_flags_lowest_exact(r[k])), colons, 4);
+                    flags_to_top_nibble(EXACT ? colon_flags(r[k]) : colon_flags_lowest_exact(r[k], one)), colons, 4);
         } else {
 #pragma unroll
             for (int k = RW - 1; k >= 0; --k)
                 colons = (colons << 4) |
-                         (mask_t)(flags_to_top_nibble(EXACT ? colon_flags(r[k]) : colon_flags_lowest_exact(r[k])) >> 28);
+                         (mask_t)(flags_to_top_nibble(EXACT ? colon_flags(r[k]) : colon_flags_lowest_exact(r[k], one)) >> 28);
         }
         // Only positions where some entry ends can match.  Dropping the others up front
         // is safe because the table is closed under cutting at inner colons: a candidate
@@ -259,7 +259,7 @@ template <int NCHUNK, bool WIDE>
 __global__ void __launch_bounds__(kMatchThreads, KAS_MATCH_MINB)
 match_count_kernel(const uint8_t *__restrict__ heads, uint64_t n_keys,
                    const uint32_t *__restrict__ tbl, uint32_t n_prefix, uint32_t n_slots,
-                   uint32_t log2_slots, unsigned long long *__restrict__ counts) {
+                   uint32_t log2_slots, uint32_t one, unsigned long long *__restrict__ counts) {
     using Cfg = MatchCfg<NCHUNK>;
     constexpr int XW = Cfg::kRecWords;
     constexpr int U = Cfg::kKeysPerThread;
@@ -289,6 +289,7 @@ match_count_kernel(const uint8_t *__restrict__ heads, uint64_t n_keys,
     mt.lane = threadIdx.x & 31u;
     mt.lanemask_lt = (1u << mt.lane) - 1u;
     mt.waiting = 0u;
+    mt.one = one;
     for (uint32_t i = threadIdx.x; i < n_prefix; i += blockDim.x) mt.sm.hist[i] = 0u;
     __syncthreads();
 
@@ -388,7 +389,7 @@ static int launch_match(const void *d_heads, uint64_t n_keys, const void *d_tbl,
     if (grid == 0) grid = 1;
     kern<<<(unsigned)grid, kMatchThreads, smem, stream>>>(
         static_cast<const uint8_t *>(d_heads), n_keys, static_cast<const uint32_t *>(d_tbl),
-        n_prefix, n_slots, log2_slots, reinterpret_cast<unsigned long long *>(d_counts));
+        n_prefix, n_slots, log2_slots, 1u, reinterpret_cast<unsigned long long *>(d_counts));
     KAS_CUDA_TRY(cudaGetLastError());
     return KAS_OK;
 }

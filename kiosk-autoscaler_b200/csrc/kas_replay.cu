@@ -35,6 +35,7 @@ struct ReplayParams {
     uint32_t pol_first;    // global index of pol[0]
     uint32_t pol_count;    // policies in this launch
     int32_t inprog_mode;
+    int32_t one;           // the constant 1, opaque to the compiler (see pod-tick accumulation)
     PolDev pol[kMaxPoliciesPerLaunch];
 };
 
@@ -78,6 +79,7 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
         pol[s] = P.pol[live[s] ? pbase + s : P.pol_count - 1];
     }
     const bool dense = P.dense != nullptr;
+    const int32_t one = P.one;
 
     int32_t cur[SP][VEC];
     long long pt[SP][VEC];
@@ -112,7 +114,10 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
                     }
                     np[s][v] += (want != c);                                              // :227
                     cur[s][v] = want;
-                    pt[s][v] += want;
+                    // pod_ticks += want as ONE 64-bit multiply-add on the FMA pipe (want * 1 + pt)
+                    // instead of an add/add-with-carry pair on the integer ALU pipe, which is
+                    // what limits this kernel under a policy sweep
+                    pt[s][v] = (long long)want * (long long)one + pt[s][v];
                 }
                 if (dense && live[s]) {
                     int32_t *o = P.dense + ((uint64_t)(P.pol_first + pbase + s) * T + t) * P.R + r0;
@@ -430,6 +435,7 @@ int kas_replay(const kas_replay_args *a, void *stream_v) {
         P.pol_count = a->n_policies - first < (uint32_t)kMaxPoliciesPerLaunch
                           ? a->n_policies - first : (uint32_t)kMaxPoliciesPerLaunch;
         P.inprog_mode = a->inprog_mode;
+        P.one = 1;
         for (uint32_t s = 0; s < (uint32_t)kMaxPoliciesPerLaunch; ++s) {
             PolDev d = {0, 0, 0, 0, 0u};
             if (s < P.pol_count) d = make_poldev(a->policies[first + s]);
