@@ -56,6 +56,24 @@ class ReplayResult(object):
         return out
 
 
+def sweep_report(result, interval_seconds=5, cost_per_pod_hour=1.0):
+    """Per-policy summary of a replay: box-wide pod-hours (pod_ticks x INTERVAL / 3600,
+    INTERVAL as in scale.py:84), cost, number of patch calls (churn) and whether the
+    policy is on the cost / churn Pareto front.  All derived on the host from the
+    integer sums, so the report is identical at every world size."""
+    rows = []
+    for (kpp, mn, mx), s in zip(result.policies, result.sums):
+        hours = int(s[0]) * interval_seconds / 3600.0
+        rows.append(dict(keys_per_pod=kpp, min_pods=mn, max_pods=mx, pod_ticks=int(s[0]),
+                         pod_hours=hours, cost=hours * cost_per_pod_hour, n_patches=int(s[1]),
+                         final_pods=int(s[2])))
+    for a in rows:
+        a['pareto'] = not any(
+            (b['pod_ticks'] <= a['pod_ticks'] and b['n_patches'] <= a['n_patches'] and
+             (b['pod_ticks'] < a['pod_ticks'] or b['n_patches'] < a['n_patches'])) for b in rows)
+    return rows
+
+
 def _check_type(resource_type, managed=('deployment', 'job')):
     if resource_type not in managed:
         raise ValueError('`resource_type` must be one of {}. Got {}.'.format(set(managed), resource_type))

@@ -297,6 +297,73 @@ replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
     }
 }
 
+// ---- small fleets: one warp per resource, lanes are policies ------------------
+// A handful of resources (one reference pod manages ONE) cannot fill the machine
+// with a thread per resource, and a lone thread pays a full memory round trip per
+// tick.  Here a warp owns one resource: the lanes load a tile of ticks of its
+// queues into shared memory together, then every lane replays the tile for its own
+// policy out of shared memory (all lanes read the same word: a broadcast).
+constexpr int kSmallTileElems = 2048;      // trace elements per tile and warp (8 KB, twice with a per-tick in-progress trace)
+constexpr uint64_t kSmallMaxResources = 4096;
+
+template <int MODE>
+__global__ void __launch_bounds__(32)
+replay_small_kernel(const __grid_constant__ ReplayParams P) {
+    __shared__ int32_t s_l[kSmallTileElems];
+    __shared__ int32_t s_i[kSmallTileElems];
+    const uint64_t r = blockIdx.x;
+    const uint32_t lane = threadIdx.x;
+    const bool live = lane < P.pol_count;
+    const PolDev pol = P.pol[live ? lane : 0];
+    const uint64_t q0 = P.group_off ? P.group_off[r] : r;
+    const uint32_t nq = (uint32_t)((P.group_off ? P.group_off[r + 1] : r + 1) - q0);
+    const uint32_t T = P.T;
+    const uint32_t tile_ticks = nq ? kSmallTileElems / nq : T;
+    int32_t cur = P.cur0 ? P.cur0[r] : 0;
+    long long pt = 0;
+    uint32_t np = 0;
+    for (uint32_t t0 = 0; t0 < T; t0 += tile_ticks) {
+        const uint32_t nt = min(tile_ticks, T - t0);
+        const uint32_t elems = nt * nq;
+        __syncwarp();
+        for (uint32_t e = lane; e < elems; e += 32) {
+            const uint32_t t = e / nq, j = e - t * nq;
+            const uint64_t g = (uint64_t)(t0 + t) * P.Q + q0 + j;
+            s_l[e] = ldg_stream_i32(P.llen + g);
+            s_i[e] = P.inprog_mode == 2 ? ldg_stream_i32(P.inprog + g)
+                                        : (P.inprog_mode == 1 ? __ldg(P.inprog + q0 + j) : 0);
+        }
+        __syncwarp();
+        if (live) {
+            for (uint32_t t = 0; t < nt; ++t) {
+                long long sum = 0;
+                for (uint32_t j = 0; j < nq; ++j)
+                    sum += decide<MODE>(s_l[t * nq + j], s_i[t * nq + j], pol, cur);      // :255-257
+                const int32_t want = clip64(sum, pol.mn, pol.mx, cur);                    // :259
+                np += (want != cur);                                                      // :227
+                cur = want;
+                pt += want;
+                if (P.dense) P.dense[((uint64_t)(P.pol_first + lane) * T + t0 + t) * P.R + r] = want;
+            }
+        }
+    }
+    if (live) {
+        if (P.totals) {
+            kas_totals o;
+            o.pod_ticks = pt;
+            o.n_patches = np;
+            o.final_current = cur;
+            P.totals[r * P.S + P.pol_first + lane] = o;
+        }
+        if (P.sums) {
+            unsigned long long *o = P.sums + 3ull * (P.pol_first + lane);
+            atomicAdd(o + 0, (unsigned long long)pt);
+            atomicAdd(o + 1, (unsigned long long)np);
+            atomicAdd(o + 2, (unsigned long long)(long long)cur);
+        }
+    }
+}
+
 // ---- element-wise decision (scalar API) ------------------------------------
 __device__ __forceinline__ long long clip_ll(long long d, long long mn, long long mx, long long cur) {
     d = d > mx ? mx : (d < mn ? mn : d);
@@ -376,6 +443,11 @@ static void launch_identity(const ReplayParams &P, int mode, cudaStream_t stream
 #undef KAS_LAUNCH_ID
 }
 
+static void launch_small(const ReplayParams &P, int mode, cudaStream_t stream) {
+    if (mode != kGeneric) replay_small_kernel<kSimple><<<(unsigned)P.R, 32, 0, stream>>>(P);
+    else replay_small_kernel<kGeneric><<<(unsigned)P.R, 32, 0, stream>>>(P);
+}
+
 template <int SP>
 static void launch_grouped(const ReplayParams &P, int mode, cudaStream_t stream) {
     const uint64_t nx = (P.R + kReplayThreads - 1) / kReplayThreads;
@@ -418,6 +490,10 @@ int kas_replay(const kas_replay_args *a, void *stream_v) {
                       (a->inprog_mode != 1 || aligned(a->d_inprog, 4)) &&
                       (!a->d_dense || aligned(a->d_dense, 16)) && a->n_resources >= 4096;
 
+    // few resources: a warp per resource with its queues staged in shared memory
+    // (needs every resource's queues of one tick to fit a tile)
+    const bool small = a->n_resources <= kSmallMaxResources &&
+                       (identity || a->n_queues <= (uint64_t)kSmallTileElems);
     for (uint32_t first = 0; first < a->n_policies; first += kMaxPoliciesPerLaunch) {
         ReplayParams P;
         P.llen = a->d_llen;
@@ -441,7 +517,9 @@ int kas_replay(const kas_replay_args *a, void *stream_v) {
             if (s < P.pol_count) d = make_poldev(a->policies[first + s]);
             P.pol[s] = d;
         }
-        if (identity) {
+        if (small) {
+            launch_small(P, mode, stream);
+        } else if (identity) {
             if (P.pol_count == 1) {
                 if (vec4) launch_identity<4, 1>(P, mode, stream);
                 else launch_identity<1, 1>(P, mode, stream);

@@ -46,6 +46,13 @@ def test_c1_reference_run():
     for k, si in enumerate(g['dense_idx']):
         assert (res.dense[si, :, 0] == g['dense'][k]).all()
     assert res.sums[:, 0].tolist() == g['pod_ticks'].tolist()
+    rep = autoscaler.replay.sweep_report(res, interval_seconds=5, cost_per_pod_hour=2.0)
+    assert [r['pod_ticks'] for r in rep] == g['pod_ticks'].tolist()
+    assert [r['n_patches'] for r in rep] == g['n_patches'].tolist()
+    assert rep[0]['pod_hours'] == g['pod_ticks'][0] * 5 / 3600.0 and rep[0]['cost'] == 2 * rep[0]['pod_hours']
+    front = [r for r in rep if r['pareto']]
+    assert front and all(not (o['pod_ticks'] < f['pod_ticks'] and o['n_patches'] < f['n_patches'])
+                         for f in front for o in rep)
 
 
 POLICY_SETS = {
@@ -59,14 +66,16 @@ POLICY_SETS = {
 
 
 @pytest.mark.parametrize('pol', list(POLICY_SETS))
-@pytest.mark.parametrize('shape', ['vec4', 'scalar', 'grouped', 'tiny'])
+@pytest.mark.parametrize('shape', ['vec4', 'scalar', 'grouped', 'tiny', 'small_grouped', 'small_identity'])
 @pytest.mark.parametrize('ipmode', [0, 1, 2])
 def test_random_fleets_vs_oracle(pol, shape, ipmode):
     import autoscaler
     from oracle import coracle
     rng = np.random.default_rng(hash((pol, shape, ipmode)) % (2 ** 32))
-    T, Q = {'vec4': (37, 8192), 'scalar': (50, 4099), 'grouped': (41, 3000), 'tiny': (300, 3)}[shape]
-    llen, go = helpers.random_fleet(rng, T, Q, grouped=(shape == 'grouped'), neg=(pol == 'negative'))
+    T, Q = {'vec4': (37, 8192), 'scalar': (50, 4099), 'grouped': (41, 3000), 'tiny': (300, 3),
+            'small_grouped': (700, 1500), 'small_identity': (130, 2048)}[shape]
+    llen, go = helpers.random_fleet(rng, T, Q, grouped=shape in ('grouped', 'small_grouped'),
+                                    neg=(pol == 'negative'))
     if pol == 'quirks':
         llen[rng.random(llen.shape) < 0.01] = 2 ** 31 - 1
     inprog = None
