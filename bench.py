@@ -320,6 +320,41 @@ def run_ours(args):
                    'H2D -> kas_match_count_accumulate -> counts D2H'}
     del streamer
 
+    # ---- ingest: variable-length keys -> packed heads (long-tailed lengths, C5-like) ------
+    ingest = None
+    if rank == 0 and not args.no_cpu:
+        n_ing = int(os.environ.get('KAS_BENCH_INGEST_KEYS', 16_000_000))
+        _, iblob, ioff = engine.synth_keys_host(SEED + 7, 0, n_ing, names, long_tail=True,
+                                                want_heads=False, want_blob=True)
+        t0 = time.perf_counter()
+        hh = engine.pack_heads_host(iblob, ioff, W)
+        host_s = time.perf_counter() - t0
+        d_blob = torch.from_numpy(iblob).to(dev)
+        d_off = torch.from_numpy(ioff.view(np.int64)).to(dev)
+        for _ in range(3):
+            dh = engine.pack_heads_device(d_blob, d_off, n_ing, W)
+        torch.cuda.synchronize()
+        i0, i1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        i0.record()
+        for _ in range(10):
+            dh = engine.pack_heads_device(d_blob, d_off, n_ing, W)
+        i1.record()
+        torch.cuda.synchronize()
+        pack_ms = i0.elapsed_time(i1) / 10
+        same = bool((dh.cpu().numpy() == hh).all())
+        if not same:
+            raise SystemExit('bench.py: device and host head packers disagree')
+        ing_bytes = int(iblob.size) + 8 * (n_ing + 1) + n_ing * W
+        ingest = {'keys': n_ing, 'mean_key_bytes': float(iblob.size) / n_ing,
+                  'device_pack': {'ms': pack_ms, 'keys_per_sec': n_ing / (pack_ms * 1e-3),
+                                  'roofline': {'bound': 'hbm', 'achieved': ing_bytes / (pack_ms * 1e-3) / 1e9,
+                                               'peak': peak, 'unit': 'GB/s',
+                                               'frac': ing_bytes / (pack_ms * 1e-3) / 1e9 / peak,
+                                               'algorithmic_bytes_per_launch': ing_bytes}},
+                  'host_pack': {'keys_per_sec': n_ing / host_s, 'threads': engine.host_threads()},
+                  'device_equals_host': same}
+        del d_blob, d_off, dh, hh, iblob, ioff
+
     # ---- replay (K2), BASELINE config 3 per GPU -------------------------------------
     rep = None
     if not args.no_replay:
@@ -396,7 +431,7 @@ def run_ours(args):
             'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'u8',
             'data': 'synthetic', 'config': bench_config(world), 'roofline': roofline,
             'cpu_baseline': cpu, 'e2e': e2e, 'gpu_launches': args.steps, 'clocks': clocks,
-            'replay': rep,
+            'replay': rep, 'ingest': ingest,
             'checks': {'keys_matched_fraction': float(counts_box.sum()) / (world * n),
                        'host_generation_s': gen_s,
                        'local_counts_sum': int(local_counts.sum())},
