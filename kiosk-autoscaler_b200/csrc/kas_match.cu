@@ -26,7 +26,7 @@
 namespace kas {
 
 #ifndef KAS_MATCH_U
-#define KAS_MATCH_U 4      // keys per thread per step (32-byte records)
+#define KAS_MATCH_U 2      // keys per thread per step (32-byte records); two steps are in flight
 #endif
 #ifndef KAS_MATCH_MINB
 #define KAS_MATCH_MINB 4   // resident blocks per SM the register budget is held to
@@ -63,7 +63,8 @@ struct MatchCfg {
     static constexpr int kRWP = (kRW + 3) / 4 * 4;                         // padded to 128-bit rows
     static constexpr int kEW = kRW + 2;                                    // entry words
     static constexpr int kRows = 16 * NCHUNK - (int)kRegionStart;           // colon positions inside the region
-    static constexpr int kKeysPerThread = NCHUNK <= 2 ? KAS_MATCH_U : 2;
+    static constexpr int kKeysPerThread = NCHUNK <= 2 ? KAS_MATCH_U : 1;
+    static constexpr int kMinBlocks = NCHUNK <= 2 ? KAS_MATCH_MINB : 3;    // wide records need the registers
     using mask_t = typename std::conditional<(kRows <= 32), uint32_t, uint64_t>::type;   // one bit per colon position
     // a deferred walk: region words + the position already dealt with, padded to 128-bit rows
     static constexpr int kItemWords = (kRW + 1 + 3) / 4 * 4;
@@ -256,7 +257,7 @@ struct Matcher {
 };
 
 template <int NCHUNK, bool WIDE>
-__global__ void __launch_bounds__(kMatchThreads, KAS_MATCH_MINB)
+__global__ void __launch_bounds__(kMatchThreads, MatchCfg<NCHUNK>::kMinBlocks)
 match_count_kernel(const uint8_t *__restrict__ heads, uint64_t n_keys,
                    const uint32_t *__restrict__ tbl, uint32_t n_prefix, uint32_t n_slots,
                    uint32_t log2_slots, uint32_t one, unsigned long long *__restrict__ counts) {
@@ -293,9 +294,10 @@ match_count_kernel(const uint8_t *__restrict__ heads, uint64_t n_keys,
     for (uint32_t i = threadIdx.x; i < n_prefix; i += blockDim.x) mt.sm.hist[i] = 0u;
     __syncthreads();
 
-    const uint64_t tile = (uint64_t)blockDim.x * U;
-    for (uint64_t base = (uint64_t)blockIdx.x * tile; base < n_keys; base += (uint64_t)gridDim.x * tile) {
-        uint32_t x[U][XW];
+    // U records per thread and step; the next step's records are already in flight
+    // while this step's are examined (two register buffers, the loop is unrolled by two
+    // so that they never have to be copied).
+    auto load_tile = [&](uint64_t base, uint32_t (&x)[U][XW]) {
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             const uint64_t idx = base + (uint64_t)u * blockDim.x + threadIdx.x;
@@ -325,17 +327,38 @@ match_count_kernel(const uint8_t *__restrict__ heads, uint64_t n_keys,
                 for (int j = 0; j < XW; ++j) x[u][j] = 0u;
             }
         }
+    };
+    // The warp histogram of record u is issued (MATCH.ANY) as soon as its queue id is
+    // known and consumed one record later, so its latency hides behind the next lookup.
+    uint32_t pend_q = kNoQueue, pend_peers = 0u;
+    auto settle = [&]() {
+        if (pend_q != kNoQueue && (pend_peers & mt.lanemask_lt) == 0u)   // lowest lane of each group adds
+            atomicAdd(&mt.sm.hist[pend_q], (uint32_t)__popc(pend_peers));
+    };
+    auto examine = [&](const uint32_t (&x)[U][XW]) {
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             const uint32_t q = mt.first_step(x[u]);
-            if (__any_sync(0xFFFFFFFFu, q != kNoQueue)) {
-                // warp histogram: lanes holding the same queue elect one adder
-                const uint32_t peers = __match_any_sync(0xFFFFFFFFu, q);
-                if (q != kNoQueue && (peers & mt.lanemask_lt) == 0u)
-                    atomicAdd(&mt.sm.hist[q], (uint32_t)__popc(peers));
-            }
+            settle();
+            pend_q = q;
+            pend_peers = __match_any_sync(0xFFFFFFFFu, q);
         }
+    };
+    const uint64_t tile = (uint64_t)blockDim.x * U;
+    const uint64_t stride = (uint64_t)gridDim.x * tile;
+    uint64_t base = (uint64_t)blockIdx.x * tile;
+    uint32_t xa[U][XW], xb[U][XW];
+    if (base < n_keys) load_tile(base, xa);
+    while (base < n_keys) {
+        load_tile(base + stride, xb);          // past the end: zero records, no loads
+        examine(xa);
+        base += stride;
+        if (base >= n_keys) break;
+        load_tile(base + stride, xa);
+        examine(xb);
+        base += stride;
     }
+    settle();
     while (mt.waiting) mt.resume();
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < n_prefix; i += blockDim.x) {
