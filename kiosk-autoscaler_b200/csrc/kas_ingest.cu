@@ -53,8 +53,10 @@ static void parallel_for(uint64_t n, int threads, F fn) {
     for (auto &th : pool) th.join();
 }
 
-// One thread per 16-byte chunk of the output; byte loads from the blob go
-// through L1 (neighbouring threads read neighbouring bytes).
+// One thread per 16-byte chunk of the output.  The chunk's source bytes sit at an
+// arbitrary byte address, so the thread reads the (up to five) aligned 32-bit words
+// that cover them and funnel-shifts them into place; bytes past the key's end are
+// masked to zero and words that lie wholly past it are not read at all.
 __global__ void __launch_bounds__(256)
 pack_heads_kernel(const uint8_t *__restrict__ blob, const uint64_t *__restrict__ off,
                   uint64_t n_keys, uint32_t sep_bytes, uint32_t chunks, uint4 *__restrict__ heads) {
@@ -62,15 +64,28 @@ pack_heads_kernel(const uint8_t *__restrict__ blob, const uint64_t *__restrict__
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (uint64_t)gridDim.x * blockDim.x) {
         const uint64_t key = i / chunks;
-        const uint32_t c = (uint32_t)(i % chunks);
-        const uint64_t a = off[key], b = off[key + 1];
+        const uint32_t c = (uint32_t)(i - key * chunks);
+        const uint64_t a = __ldg(off + key), b = __ldg(off + key + 1);
         const uint64_t len = (b - a) > sep_bytes ? (b - a) - sep_bytes : 0;
         const uint64_t lo = 16ull * c;
         uint32_t w[4] = {0u, 0u, 0u, 0u};
         if (len > lo) {
-            const uint32_t n = (uint32_t)(len - lo < 16 ? len - lo : 16);
-            const uint8_t *p = blob + a + lo;
-            for (uint32_t j = 0; j < n; ++j) w[j >> 2] |= (uint32_t)p[j] << (8 * (j & 3));
+            const uint32_t n = (uint32_t)(len - lo < 16 ? len - lo : 16);   // valid bytes, 1..16
+            const uintptr_t addr = reinterpret_cast<uintptr_t>(blob) + a + lo;
+            const uint32_t *wp = reinterpret_cast<const uint32_t *>(addr & ~(uintptr_t)3);
+            const uint32_t mis = (uint32_t)(addr & 3u);                     // bytes to drop from word 0
+            const uint32_t need = (mis + n + 3u) >> 2;                      // aligned words touched, 1..5
+            uint32_t v[5];
+#pragma unroll
+            for (int j = 0; j < 5; ++j) v[j] = (uint32_t)j < need ? __ldg(wp + j) : 0u;
+            const uint32_t sh = mis * 8u;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t x = __funnelshift_r(v[j], v[j + 1], sh);
+                const int rem = (int)n - 4 * j;                             // valid bytes of this word
+                const uint32_t m = rem >= 4 ? 0xFFFFFFFFu : (rem <= 0 ? 0u : (0xFFFFFFFFu >> (32 - 8 * rem)));
+                w[j] = x & m;
+            }
         }
         heads[i] = make_uint4(w[0], w[1], w[2], w[3]);
     }
