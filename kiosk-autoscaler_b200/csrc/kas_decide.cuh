@@ -65,21 +65,27 @@ __device__ __forceinline__ int32_t decide_exact(int32_t llen, int32_t inprog, co
     return clip64(floordiv_any((int64_t)llen + (int64_t)inprog, p), p.mn, p.mx, cur);
 }
 
-// The same for kpp >= 1, min <= max, max >= 0 and a tally in [0, 2^32).
+// The same for kpp >= 1, min <= max, max >= 0 and a tally in [0, 2^32), in two
+// halves: the quotient depends on keys_per_pod alone (policies of a sweep that share
+// it share the quotient), the rest on min / max / current pods.
 template <bool K1>
-__device__ __forceinline__ int32_t decide_simple(uint32_t tally, const PolDev &p, int32_t cur) {
-    uint32_t q = tally;
-    if (!K1) {
-        // floor(tally / kpp) = high 64 bits of magic * tally (the quotient fits 32 bits);
-        // kpp == 1 has magic == 0 and k1 == 1, so the same multiply-adds give q = tally
-        const uint32_t lo_hi = __umulhi((uint32_t)p.magic, tally);
-        const uint32_t mh = (uint32_t)(((uint64_t)(uint32_t)(p.magic >> 32) * tally + lo_hi) >> 32);
-        q = tally * p.k1 + mh;
-    }
+__device__ __forceinline__ uint32_t quotient_simple(uint32_t tally, const PolDev &p) {
+    if (K1) return tally;
+    // floor(tally / kpp) = high 64 bits of magic * tally (the quotient fits 32 bits);
+    // kpp == 1 has magic == 0 and k1 == 1, so the same multiply-adds give q = tally
+    const uint32_t lo_hi = __umulhi((uint32_t)p.magic, tally);
+    const uint32_t mh = (uint32_t)(((uint64_t)(uint32_t)(p.magic >> 32) * tally + lo_hi) >> 32);
+    return tally * p.k1 + mh;
+}
+__device__ __forceinline__ int32_t finish_simple(uint32_t q, const PolDev &p, int32_t cur) {
     // if/elif clamp with 0 <= max and min <= max: the unsigned min already lands in
     // [0, max], so no saturation of q is needed before the signed max with min
     const int32_t d = max((int32_t)min(q, (uint32_t)p.mx), p.mn);
     return d > 0 ? max(d, cur) : d;
+}
+template <bool K1>
+__device__ __forceinline__ int32_t decide_simple(uint32_t tally, const PolDev &p, int32_t cur) {
+    return finish_simple(quotient_simple<K1>(tally, p), p, cur);
 }
 
 template <int MODE>

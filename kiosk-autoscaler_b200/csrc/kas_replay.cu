@@ -13,6 +13,8 @@
 #include "kas_decide.cuh"
 
 #include <limits.h>
+#include <algorithm>
+#include <vector>
 #include <type_traits>
 
 namespace kas {
@@ -36,8 +38,26 @@ struct ReplayParams {
     uint32_t pol_count;    // policies in this launch
     int32_t inprog_mode;
     int32_t one;           // the constant 1, opaque to the compiler (see pod-tick accumulation)
+    uint16_t pol_index[kMaxPoliciesPerLaunch];   // slot -> index of the policy in the caller's list
     PolDev pol[kMaxPoliciesPerLaunch];
 };
+
+// n += (a != b) as a compare and a predicated add (two instructions).
+__device__ __forceinline__ void count_if_ne(uint32_t &n, int32_t a, int32_t b) {
+    asm("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %1, %2;\n\t@p add.u32 %0, %0, 1;\n\t}" : "+r"(n) : "r"(a), "r"(b));
+}
+
+#ifndef KAS_PT_WIDE
+#define KAS_PT_WIDE 1   // pod_ticks += want as one IMAD.WIDE (1) or as a 64-bit add (0)
+#endif
+__device__ __forceinline__ void add_pod_ticks(long long &pt, int32_t want, int32_t one) {
+#if KAS_PT_WIDE
+    pt = (long long)want * (long long)one + pt;
+#else
+    (void)one;
+    pt += want;
+#endif
+}
 
 __device__ __forceinline__ long long warp_sum_ll(long long v) {
 #pragma unroll
@@ -112,7 +132,7 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
                         want = decide_exact(l[v], IPMODE == 0 ? 0 : ip[v], pol[s], c);    // :255-257
                         want = clip32(want, pol[s].mn, pol[s].mx, c);                     // :259
                     }
-                    np[s][v] += (want != c);                                              // :227
+                    count_if_ne(np[s][v], want, c);                                       // :227
                     cur[s][v] = want;
                     // pod_ticks += want as ONE 64-bit multiply-add on the FMA pipe (want * 1 + pt)
                     // instead of an add/add-with-carry pair on the integer ALU pipe, which is
@@ -120,7 +140,7 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
                     pt[s][v] = (long long)want * (long long)one + pt[s][v];
                 }
                 if (dense && live[s]) {
-                    int32_t *o = P.dense + ((uint64_t)(P.pol_first + pbase + s) * T + t) * P.R + r0;
+                    int32_t *o = P.dense + ((uint64_t)P.pol_index[pbase + s] * T + t) * P.R + r0;
                     if constexpr (VEC == 4)
                         *reinterpret_cast<int4 *>(o) = make_int4(cur[s][0], cur[s][1], cur[s][2], cur[s][3]);
                     else
@@ -198,7 +218,7 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
                         o.pod_ticks = pt[s][v];
                         o.n_patches = np[s][v];
                         o.final_current = cur[s][v];
-                        P.totals[(r0 + v) * P.S + P.pol_first + pbase + s] = o;
+                        P.totals[(r0 + v) * P.S + P.pol_index[pbase + s]] = o;
                     }
         }
     }
@@ -213,7 +233,7 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
                 }
                 a = warp_sum_ll(a); b = warp_sum_ll(b); c = warp_sum_ll(c);
                 if ((threadIdx.x & 31) == 0) {
-                    unsigned long long *o = P.sums + 3ull * (P.pol_first + pbase + s);
+                    unsigned long long *o = P.sums + 3ull * P.pol_index[pbase + s];
                     atomicAdd(o + 0, (unsigned long long)a);
                     atomicAdd(o + 1, (unsigned long long)b);
                     atomicAdd(o + 2, (unsigned long long)c);
@@ -264,7 +284,7 @@ replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
                     np[s] += (want != cur[s]);
                     cur[s] = want;
                     pt[s] += want;
-                    if (P.dense) P.dense[((uint64_t)(P.pol_first + pbase + s) * T + t) * P.R + r] = want;
+                    if (P.dense) P.dense[((uint64_t)P.pol_index[pbase + s] * T + t) * P.R + r] = want;
                 }
             }
         }
@@ -276,7 +296,7 @@ replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
                     o.pod_ticks = pt[s];
                     o.n_patches = np[s];
                     o.final_current = cur[s];
-                    P.totals[r * P.S + P.pol_first + pbase + s] = o;
+                    P.totals[r * P.S + P.pol_index[pbase + s]] = o;
                 }
         }
     }
@@ -287,7 +307,209 @@ replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
                 long long a = valid ? pt[s] : 0, b = valid ? (long long)np[s] : 0, c = valid ? (long long)cur[s] : 0;
                 a = warp_sum_ll(a); b = warp_sum_ll(b); c = warp_sum_ll(c);
                 if ((threadIdx.x & 31) == 0) {
-                    unsigned long long *o = P.sums + 3ull * (P.pol_first + pbase + s);
+                    unsigned long long *o = P.sums + 3ull * P.pol_index[pbase + s];
+                    atomicAdd(o + 0, (unsigned long long)a);
+                    atomicAdd(o + 1, (unsigned long long)b);
+                    atomicAdd(o + 2, (unsigned long long)c);
+                }
+            }
+        }
+    }
+}
+
+// ---- policy sweeps over single-queue resources: the trace is read ONCE ---------
+// Under a sweep every policy needs the same trace element.  A block owns a run of
+// adjacent resources and ALL policies of the launch: its threads stage tiles of the
+// trace in shared memory with asynchronous copies (cp.async, three tile buffers, one
+// block barrier per tile) and every warp replays the tile for two policies and 128
+// resources out of shared memory.  DRAM traffic is the trace itself, whatever the
+// number of policies; the kernel is then bound by the integer pipes alone.
+// A block always has about 16 warps (4 per scheduler): with C policy pairs it covers
+// floor(16 / C) groups of 128 resources, and a tile holds 2048 / groups ticks.
+constexpr int kSweepCols = 128;                 // resources per block (32 lanes x 4)
+constexpr int kSweepTileRows = 64;              // ticks per tile when a block covers one group of columns
+constexpr int kSweepStages = 3;                 // tiles in shared memory (one block barrier per tile)
+constexpr int kSweepSP = 2;                     // policies per warp
+constexpr int kSweepMaxWarps = kMaxPoliciesPerLaunch / kSweepSP;   // 16
+
+__device__ __forceinline__ void cp_async_16(void *smem_dst, const void *gmem_src) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+template <bool TICKIP, int MODE>
+__global__ void __launch_bounds__(32 * kSweepMaxWarps, 1)
+replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
+    constexpr int SP = kSweepSP, VEC = 4;
+    extern __shared__ int4 sweep_smem[];            // [TICKIP ? 2 : 1][kSweepStages][ticks][groups][32] int4
+    constexpr int kTileVec = kSweepTileRows * 32;   // int4 per tile and array, whatever the split
+    int4 *s_l = sweep_smem;                                  // llen tiles
+    int4 *s_i = sweep_smem + kSweepStages * kTileVec;        // in-progress tiles (TICKIP only)
+
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t chunks = (P.pol_count + SP - 1) / SP;          // policy pairs in this launch
+    const uint32_t groups = blockDim.x / (32u * chunks);          // column groups of the block
+    const uint32_t tile_ticks = kSweepTileRows / groups;
+    const uint32_t pbase = (warp % chunks) * SP;
+    const uint32_t cg = warp / chunks;
+    const uint64_t col0 = (uint64_t)blockIdx.x * groups * kSweepCols;     // first resource of the block
+    const uint64_t r0 = col0 + (uint64_t)cg * kSweepCols + 4ull * lane;
+    const bool valid = r0 < P.R;
+    const uint32_t T = P.T;
+    const uint64_t Q = P.Q;
+    const uint32_t row_vec = groups * 32u;                                   // int4 per staged tick
+    const uint32_t vec_here = (uint32_t)(min((uint64_t)groups * kSweepCols, P.R - col0) / 4);   // R % 4 == 0
+
+    PolDev pol[SP];
+    bool live[SP];
+#pragma unroll
+    for (int s = 0; s < SP; ++s) {
+        live[s] = pbase + s < P.pol_count;
+        pol[s] = P.pol[live[s] ? pbase + s : P.pol_count - 1];
+    }
+    const bool dense = P.dense != nullptr;
+    const int32_t one = P.one;
+    const bool same_kpp = pol[0].magic == pol[SP - 1].magic && pol[0].k1 == pol[SP - 1].k1;
+    int32_t cur[SP][VEC];
+    long long pt[SP][VEC];
+    uint32_t np[SP][VEC];
+    int32_t ipq[VEC];
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) {
+        const int32_t c0 = (valid && P.cur0) ? P.cur0[r0 + v] : 0;
+        ipq[v] = (valid && P.inprog_mode == 1) ? P.inprog[r0 + v] : 0;
+#pragma unroll
+        for (int s = 0; s < SP; ++s) { cur[s][v] = c0; pt[s][v] = 0; np[s][v] = 0u; }
+    }
+
+    // stage tile `k` into buffer k % kSweepStages: every thread copies 16-byte pieces
+    const uint32_t n_tiles = (T + tile_ticks - 1) / tile_ticks;
+    auto stage = [&](uint32_t k) {
+        if (k < n_tiles) {
+            const uint32_t t0 = k * tile_ticks;
+            const uint32_t nt = min(tile_ticks, T - t0);
+            int4 *dl = s_l + (k % kSweepStages) * kTileVec;
+            int4 *di = s_i + (k % kSweepStages) * kTileVec;
+            for (uint32_t e = threadIdx.x; e < nt * row_vec; e += blockDim.x) {
+                const uint32_t t = e / row_vec, c = e - t * row_vec;
+                if (c < vec_here) {
+                    const uint64_t g = (uint64_t)(t0 + t) * Q + col0 + 4ull * c;
+                    cp_async_16(dl + e, P.llen + g);
+                    if (TICKIP) cp_async_16(di + e, P.inprog + g);
+                }
+            }
+        }
+        cp_async_commit();
+    };
+    stage(0);
+    stage(1);
+    for (uint32_t k = 0; k < n_tiles; ++k) {
+        cp_async_wait<1>();            // this thread's pieces of tile k have landed
+        __syncthreads();               // ... and everybody else's; all are done with tile k-1
+        stage(k + 2);                  // refill the buffer tile k-1 occupied
+        const uint32_t t0 = k * tile_ticks;
+        const uint32_t nt = min(tile_ticks, T - t0);
+        const int4 *tl = s_l + (k % kSweepStages) * kTileVec + cg * 32u + lane;
+        const int4 *ti = s_i + (k % kSweepStages) * kTileVec + cg * 32u + lane;
+        if (valid && (live[0] || live[SP - 1])) {
+            // G ticks at a time: their rows are read from shared memory first, one sign
+            // test picks the arithmetic for all of them, then the recurrences run
+            auto ticks = [&](uint32_t t, auto gtag) {
+                constexpr int G = decltype(gtag)::value;
+                int32_t l[G][VEC], ip[G][VEC];
+                int32_t any = 0;
+#pragma unroll
+                for (int g = 0; g < G; ++g) {
+                    const int4 a = tl[(t + g) * row_vec];
+                    l[g][0] = a.x; l[g][1] = a.y; l[g][2] = a.z; l[g][3] = a.w;
+                    if (TICKIP) {
+                        const int4 b = ti[(t + g) * row_vec];
+                        ip[g][0] = b.x; ip[g][1] = b.y; ip[g][2] = b.z; ip[g][3] = b.w;
+                    } else {
+#pragma unroll
+                        for (int v = 0; v < VEC; ++v) ip[g][v] = ipq[v];
+                    }
+#pragma unroll
+                    for (int v = 0; v < VEC; ++v) any |= l[g][v] | ip[g][v];
+                }
+                auto run = [&](auto fasttag, auto sametag) {
+                    constexpr bool FAST = decltype(fasttag)::value;
+                    constexpr bool SAMEK = decltype(sametag)::value;   // both policies divide by the same kpp
+#pragma unroll
+                    for (int g = 0; g < G; ++g) {
+                        uint32_t q0[VEC];
+                        if constexpr (FAST && SAMEK) {
+#pragma unroll
+                            for (int v = 0; v < VEC; ++v)
+                                q0[v] = quotient_simple<false>((uint32_t)l[g][v] + (uint32_t)ip[g][v], pol[0]);
+                        }
+#pragma unroll
+                        for (int s = 0; s < SP; ++s) {
+#pragma unroll
+                            for (int v = 0; v < VEC; ++v) {
+                                const int32_t c = cur[s][v];
+                                int32_t want;
+                                if constexpr (FAST && SAMEK) {
+                                    want = finish_simple(q0[v], pol[s], c);                                           // :255-259
+                                } else if constexpr (FAST) {
+                                    want = decide_simple<false>((uint32_t)l[g][v] + (uint32_t)ip[g][v], pol[s], c);   // :255-259
+                                } else {
+                                    want = decide_exact(l[g][v], ip[g][v], pol[s], c);                                 // :255-257
+                                    want = clip32(want, pol[s].mn, pol[s].mx, c);                                     // :259
+                                }
+                                count_if_ne(np[s][v], want, c);                                                       // :227
+                                cur[s][v] = want;
+                                add_pod_ticks(pt[s][v], want, one);
+                            }
+                            if (dense && live[s]) {
+                                int32_t *o = P.dense + ((uint64_t)P.pol_index[pbase + s] * T + t0 + t + g) * P.R + r0;
+                                *reinterpret_cast<int4 *>(o) = make_int4(cur[s][0], cur[s][1], cur[s][2], cur[s][3]);
+                            }
+                        }
+                    }
+                };
+                if (MODE != kGeneric && any >= 0) {
+                    if (same_kpp) run(std::true_type{}, std::true_type{});
+                    else run(std::true_type{}, std::false_type{});
+                } else {
+                    run(std::false_type{}, std::false_type{});
+                }
+            };
+            uint32_t t = 0;
+            for (; t + 4 <= nt; t += 4) ticks(t, std::integral_constant<int, 4>{});
+            for (; t < nt; ++t) ticks(t, std::integral_constant<int, 1>{});
+        }
+    }
+    cp_async_wait<0>();
+
+    if (valid && P.totals) {
+#pragma unroll
+        for (int s = 0; s < SP; ++s)
+            if (live[s])
+#pragma unroll
+                for (int v = 0; v < VEC; ++v) {
+                    kas_totals o;
+                    o.pod_ticks = pt[s][v];
+                    o.n_patches = np[s][v];
+                    o.final_current = cur[s][v];
+                    P.totals[(r0 + v) * P.S + P.pol_index[pbase + s]] = o;
+                }
+    }
+    if (P.sums) {
+#pragma unroll
+        for (int s = 0; s < SP; ++s) {
+            if (live[s]) {   // uniform across the warp
+                long long a = 0, b = 0, c = 0;
+                if (valid) {
+#pragma unroll
+                    for (int v = 0; v < VEC; ++v) { a += pt[s][v]; b += np[s][v]; c += cur[s][v]; }
+                }
+                a = warp_sum_ll(a); b = warp_sum_ll(b); c = warp_sum_ll(c);
+                if (lane == 0) {
+                    unsigned long long *o = P.sums + 3ull * P.pol_index[pbase + s];
                     atomicAdd(o + 0, (unsigned long long)a);
                     atomicAdd(o + 1, (unsigned long long)b);
                     atomicAdd(o + 2, (unsigned long long)c);
@@ -343,7 +565,7 @@ replay_small_kernel(const __grid_constant__ ReplayParams P) {
                 np += (want != cur);                                                      // :227
                 cur = want;
                 pt += want;
-                if (P.dense) P.dense[((uint64_t)(P.pol_first + lane) * T + t0 + t) * P.R + r] = want;
+                if (P.dense) P.dense[((uint64_t)P.pol_index[lane] * T + t0 + t) * P.R + r] = want;
             }
         }
     }
@@ -353,10 +575,10 @@ replay_small_kernel(const __grid_constant__ ReplayParams P) {
             o.pod_ticks = pt;
             o.n_patches = np;
             o.final_current = cur;
-            P.totals[r * P.S + P.pol_first + lane] = o;
+            P.totals[r * P.S + P.pol_index[lane]] = o;
         }
         if (P.sums) {
-            unsigned long long *o = P.sums + 3ull * (P.pol_first + lane);
+            unsigned long long *o = P.sums + 3ull * P.pol_index[lane];
             atomicAdd(o + 0, (unsigned long long)pt);
             atomicAdd(o + 1, (unsigned long long)np);
             atomicAdd(o + 2, (unsigned long long)(long long)cur);
@@ -443,6 +665,31 @@ static void launch_identity(const ReplayParams &P, int mode, cudaStream_t stream
 #undef KAS_LAUNCH_ID
 }
 
+static int launch_sweep(const ReplayParams &P, int mode, cudaStream_t stream) {
+    const bool tickip = P.inprog_mode == 2;
+    const unsigned chunks = (P.pol_count + kSweepSP - 1) / kSweepSP;          // <= 16
+    const unsigned groups = kSweepMaxWarps / chunks;                           // >= 1
+    const unsigned warps = chunks * groups;
+    const uint64_t cols_per_block = (uint64_t)groups * kSweepCols;
+    const unsigned grid = (unsigned)((P.R + cols_per_block - 1) / cols_per_block);
+    const size_t smem = (size_t)(tickip ? 2 : 1) * kSweepStages * kSweepTileRows * 32 * sizeof(int4);
+#define KAS_LAUNCH_SWEEP(TI, MD)                                                                   \
+    do {                                                                                           \
+        auto kern = replay_sweep_kernel<TI, MD>;                                                   \
+        if (smem > 48 * 1024)                                                                      \
+            KAS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
+                                              (int)smem));                                         \
+        kern<<<grid, 32 * warps, smem, stream>>>(P);                                               \
+    } while (0)
+    if (mode != kGeneric) {
+        if (tickip) KAS_LAUNCH_SWEEP(true, kSimple); else KAS_LAUNCH_SWEEP(false, kSimple);
+    } else {
+        if (tickip) KAS_LAUNCH_SWEEP(true, kGeneric); else KAS_LAUNCH_SWEEP(false, kGeneric);
+    }
+#undef KAS_LAUNCH_SWEEP
+    return KAS_OK;
+}
+
 static void launch_small(const ReplayParams &P, int mode, cudaStream_t stream) {
     if (mode != kGeneric) replay_small_kernel<kSimple><<<(unsigned)P.R, 32, 0, stream>>>(P);
     else replay_small_kernel<kGeneric><<<(unsigned)P.R, 32, 0, stream>>>(P);
@@ -494,6 +741,18 @@ int kas_replay(const kas_replay_args *a, void *stream_v) {
     // (needs every resource's queues of one tick to fit a tile)
     const bool small = a->n_resources <= kSmallMaxResources &&
                        (identity || a->n_queues <= (uint64_t)kSmallTileElems);
+    // Slots of a launch in the caller's order, except under a sweep of single-queue
+    // resources: there policies are ordered by keys_per_pod, so that the two policies a
+    // warp replays usually share it (and with it the quotient).  Results are written at
+    // the caller's indices either way.
+    std::vector<uint32_t> order(a->n_policies);
+    for (uint32_t i = 0; i < a->n_policies; ++i) order[i] = i;
+    const bool sweep_path = !small && identity && vec4 && a->n_policies > 1;
+    if (sweep_path)
+        std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) {
+            return a->policies[x].keys_per_pod < a->policies[y].keys_per_pod;
+        });
+    if (a->n_policies > 65535) return KAS_ERR_UNSUPPORTED;
     for (uint32_t first = 0; first < a->n_policies; first += kMaxPoliciesPerLaunch) {
         ReplayParams P;
         P.llen = a->d_llen;
@@ -514,8 +773,13 @@ int kas_replay(const kas_replay_args *a, void *stream_v) {
         P.one = 1;
         for (uint32_t s = 0; s < (uint32_t)kMaxPoliciesPerLaunch; ++s) {
             PolDev d = {0, 0, 0, 0, 0u};
-            if (s < P.pol_count) d = make_poldev(a->policies[first + s]);
+            uint32_t idx = 0;
+            if (s < P.pol_count) {
+                idx = order[first + s];
+                d = make_poldev(a->policies[idx]);
+            }
             P.pol[s] = d;
+            P.pol_index[s] = (uint16_t)idx;
         }
         if (small) {
             launch_small(P, mode, stream);
@@ -524,8 +788,12 @@ int kas_replay(const kas_replay_args *a, void *stream_v) {
                 if (vec4) launch_identity<4, 1>(P, mode, stream);
                 else launch_identity<1, 1>(P, mode, stream);
             } else {
-                if (vec4) launch_identity<4, KAS_REPLAY_SWEEP_SP>(P, mode, stream);
-                else launch_identity<1, 4>(P, mode, stream);
+                if (vec4) {
+                    const int st = launch_sweep(P, mode, stream);
+                    if (st != KAS_OK) return st;
+                } else {
+                    launch_identity<1, 4>(P, mode, stream);
+                }
             }
         } else {
             if (P.pol_count == 1) launch_grouped<1>(P, mode, stream);

@@ -47,3 +47,38 @@ def test_int64_corners():
                    for c in cases]
     with pytest.raises(OverflowError):
         engine.decide([2 ** 64], [1], [0], [1], [0])
+
+
+def test_randomised_decisions_full_int64_domain():
+    """20 000 seeded tuples over edge values and the whole int64 range, against the
+    Python port (whose arithmetic is Python's own unbounded ints, like the reference)."""
+    import random
+    from autoscaler import engine
+    from oracle import oracle
+    rng = random.Random(31337)
+    edges = [0, 1, -1, 2, -2, 3, 7, 10, 2 ** 31 - 1, -(2 ** 31), 2 ** 31, 2 ** 32, 2 ** 62, -(2 ** 62),
+             2 ** 63 - 1, -(2 ** 63) + 1]
+
+    def pick():
+        u = rng.random()
+        if u < 0.35:
+            return rng.choice(edges)
+        if u < 0.7:
+            return rng.randint(-60, 60)
+        return rng.randint(-(2 ** 63) + 1, 2 ** 63 - 1)
+
+    rows = []
+    while len(rows) < 20000:
+        r = (pick(), pick(), pick(), pick(), pick())
+        if r[1] != 0:
+            rows.append(r)
+    got = engine.decide(*[list(c) for c in zip(*rows)], mode=0)
+    want = [oracle.get_desired_pods(*r) for r in rows]
+    bad = [(r, g, w) for r, g, w in zip(rows, got, want) if g != w]
+    assert not bad, bad[:5]
+    got = engine.decide([r[0] for r in rows], None, [r[2] for r in rows], [r[3] for r in rows],
+                        [r[4] for r in rows], mode=1)
+    assert got == [oracle.clip_pod_count(r[0], r[2], r[3], r[4]) for r in rows]
+    # a zero divisor anywhere rejects the call, as `x // 0` raises in the reference
+    with pytest.raises(ZeroDivisionError):
+        engine.decide([5, 6], [1, 0], [0, 0], [9, 9], [0, 0], mode=0)
