@@ -132,7 +132,7 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
                         want = decide_exact(l[v], IPMODE == 0 ? 0 : ip[v], pol[s], c);    // :255-257
                         want = clip32(want, pol[s].mn, pol[s].mx, c);                     // :259
                     }
-                    count_if_ne(np[s][v], want, c);                                       // :227
+                    np[s][v] += (want != c);                                              // :227
                     cur[s][v] = want;
                     // pod_ticks += want as ONE 64-bit multiply-add on the FMA pipe (want * 1 + pt)
                     // instead of an add/add-with-carry pair on the integer ALU pipe, which is
