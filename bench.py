@@ -36,6 +36,7 @@ N_KEYS_PER_GPU = int(os.environ.get('KAS_BENCH_KEYS', 100_000_000))
 N_PREFIX = 64
 REPLAY_Q = int(os.environ.get('KAS_BENCH_REPLAY_Q', 1_000_000))
 REPLAY_T = int(os.environ.get('KAS_BENCH_REPLAY_T', 10_000))
+LONG_TAIL = os.environ.get('KAS_BENCH_LONG_TAIL', '0') == '1'   # long-tailed key lengths (BASELINE config 5)
 SEED = 2
 SWEEP = [(1, 0, 1)] + [(k, a, b) for k in (1, 2, 5, 10, 50) for a in (0, 1) for b in (1, 4, 16, 64)]
 
@@ -132,7 +133,7 @@ def cpu_tally_sample(n_sample, threads):
     from oracle import coracle
     names = queue_names()
     W = engine.rec_bytes_for(names)
-    heads, _, _ = engine.synth_keys_host(SEED, 0, n_sample, names, rec_bytes=W)
+    heads, _, _ = engine.synth_keys_host(SEED, 0, n_sample, names, long_tail=LONG_TAIL, rec_bytes=W)
     coracle.match_counts_heads(names, heads[:1000], threads=threads)
     t0 = time.perf_counter()
     counts = coracle.match_counts_heads(names, heads, threads=threads)
@@ -188,7 +189,7 @@ def run_reference(args):
 def bench_config(n_gpus):
     return {'workload': 'C2 keyspace tally: %d synthetic keys per GPU x %d queue prefixes, '
                         '32-byte heads, bit-exact vs tally_queues' % (N_KEYS_PER_GPU, N_PREFIX),
-            'keys_per_gpu': N_KEYS_PER_GPU, 'n_prefix': N_PREFIX, 'rec_bytes': 32,
+            'keys_per_gpu': N_KEYS_PER_GPU, 'n_prefix': N_PREFIX, 'rec_bytes': 32, 'long_tail_keys': LONG_TAIL,
             'sharding': 'keys split by rank, counts all-reduced (NCCL)' if n_gpus > 1 else 'none',
             'l2': 'inputs (%.1f GB per GPU) larger than the 126 MB L2; no flush needed'
                   % (N_KEYS_PER_GPU * 32 / 1e9)}
@@ -222,7 +223,7 @@ def run_ours(args):
 
     host_heads = torch.empty(n * W, dtype=torch.uint8).pin_memory()
     t0 = time.perf_counter()
-    engine.synth_keys_host(SEED, first, n, names, rec_bytes=W, heads_out=host_heads)
+    engine.synth_keys_host(SEED, first, n, names, long_tail=LONG_TAIL, rec_bytes=W, heads_out=host_heads)
     gen_s = time.perf_counter() - t0
     d_heads = torch.empty(n * W, dtype=torch.uint8, device=dev)
     d_heads.copy_(host_heads, non_blocking=True)
@@ -369,6 +370,9 @@ def run_ours(args):
             S = len(policies)
             for _ in range(warm):
                 out = engine.replay(trace, T, Q, policies, want_totals=True)
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()          # ranks enter the timed region together
             torch.cuda.synchronize()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
