@@ -194,9 +194,14 @@ typedef struct kas_totals {
     int32_t final_current; /* replicas after the last tick                      */
 } kas_totals;
 
+#define KAS_TRACE_INT32 0
+#define KAS_TRACE_UINT16 1 /* depths below 65536: half the bytes of the HBM-bound replay */
+
 typedef struct kas_replay_args {
-    const int32_t *d_llen;      /* [T][Q] tick-major LLEN trace (autoscaler.py:67) */
-    const int32_t *d_inprog;    /* SCAN-count term: NULL, [Q] or [T][Q]            */
+    const void *d_llen;         /* [T][Q] tick-major LLEN trace (autoscaler.py:67),
+                                   int32 or uint16 elements (trace_dtype)          */
+    const void *d_inprog;       /* SCAN-count term: NULL, int32 [Q], or [T][Q] of
+                                   the trace's element type                        */
     int32_t inprog_mode;        /* 0 none, 1 per queue [Q], 2 per tick [T][Q]      */
     uint32_t n_ticks;           /* T                                               */
     uint64_t n_queues;          /* Q                                               */
@@ -210,12 +215,14 @@ typedef struct kas_replay_args {
                                    n_patches, final_current (what the box-wide
                                    allreduce carries), or NULL                     */
     int32_t *d_dense;           /* [S][T][R] replicas after each tick, or NULL     */
+    int32_t trace_dtype;        /* KAS_TRACE_INT32 (0) or KAS_TRACE_UINT16          */
 } kas_replay_args;
 
 /* Domain: trace values and cur0 any int32; policies any int32 with
  * keys_per_pod != 0 (KAS_ERR_ZERO_DIVISION otherwise, nothing is launched).
- * d_llen / d_inprog / d_dense need 4-byte alignment; 16-byte alignment and
- * Q % 4 == 0 enable the vectorised path for single-queue resources.        */
+ * d_llen / d_inprog need their element's alignment, d_dense 4 bytes; 16-byte
+ * alignment and Q a multiple of 4 (int32) or 8 (uint16) enable the vectorised
+ * paths for single-queue resources.                                          */
 KAS_API int kas_replay(const kas_replay_args *args, void *stream);
 
 /* ------------------------------------------------------------------------

@@ -23,6 +23,8 @@ KAS_ERR_ZERO_DIVISION = -5
 KAS_ERR_GLOB_META = -6
 KAS_ERR_TOO_SMALL = -7
 KAS_ERR_STATIC_LIMIT = -8
+TRACE_INT32 = 0
+TRACE_UINT16 = 1
 STATIC_SCRATCH_MAX_RESOURCES = 33554432
 
 MAX_PREFIXES = 1024
@@ -67,7 +69,8 @@ class ReplayArgs(C.Structure):
                 ('n_ticks', C.c_uint32), ('n_queues', C.c_uint64), ('n_resources', C.c_uint64),
                 ('d_group_off', C.c_void_p), ('d_cur0', C.c_void_p),
                 ('policies', C.POINTER(Policy)), ('n_policies', C.c_uint32),
-                ('d_totals', C.c_void_p), ('d_sums', C.c_void_p), ('d_dense', C.c_void_p)]
+                ('d_totals', C.c_void_p), ('d_sums', C.c_void_p), ('d_dense', C.c_void_p),
+                ('trace_dtype', C.c_int32)]
 
 
 _lib = None
@@ -342,9 +345,20 @@ def decide(a, kpp, mn, mx, cur, mode=0):
     return [int(v) for v in res.tolist()]
 
 
+def trace_dtype_of(t):
+    """TRACE_INT32 / TRACE_UINT16 for a trace tensor (int16 storage is read as uint16)."""
+    torch = _torch()
+    if t.dtype == torch.int32:
+        return TRACE_INT32
+    if t.dtype in (torch.uint16, torch.int16):
+        return TRACE_UINT16
+    raise TypeError('a trace must be int32 or uint16, got %s' % (t.dtype,))
+
+
 def replay(d_llen, n_ticks, n_queues, policies, d_inprog=None, inprog_mode=0, d_group_off=None,
            n_resources=None, d_cur0=None, want_totals=True, want_sums=True, want_dense=False):
     """K2 on device tensors.  policies: sequence of (kpp, min, max).
+    The trace may be int32 or uint16 (a per-tick in-progress trace has the same type).
     Returns dict of CUDA tensors: totals (uint8 view [R][S][16]), sums int64 [S][3],
     dense int32 [S][T][R] (those requested)."""
     torch = require_cuda()
@@ -361,8 +375,11 @@ def replay(d_llen, n_ticks, n_queues, policies, d_inprog=None, inprog_mode=0, d_
     totals = torch.empty((R, S, 16), dtype=torch.uint8, device=dev) if want_totals else None
     sums = torch.empty((S, 3), dtype=torch.int64, device=dev) if want_sums else None
     dense = torch.empty((S, n_ticks, R), dtype=torch.int32, device=dev) if want_dense else None
+    dt = trace_dtype_of(d_llen)
+    if inprog_mode == 2 and trace_dtype_of(d_inprog) != dt:
+        raise TypeError('a per-tick in-progress trace must have the element type of the LLEN trace')
     args = ReplayArgs(ptr(d_llen), ptr(d_inprog), inprog_mode, n_ticks, n_queues, R,
-                      ptr(d_group_off), ptr(d_cur0), parr, S, ptr(totals), ptr(sums), ptr(dense))
+                      ptr(d_group_off), ptr(d_cur0), parr, S, ptr(totals), ptr(sums), ptr(dense), dt)
     check(lib().kas_replay(C.byref(args), stream_ptr()), 'kas_replay')
     if want_totals:
         out['totals'] = totals
@@ -385,8 +402,11 @@ def patch_events(d_llen, n_ticks, n_queues, policy, d_inprog=None, inprog_mode=0
     R = n_queues if n_resources is None else n_resources
     parr = (Policy * 1)(Policy(k, a, b))
     dev = d_llen.device
+    dt = trace_dtype_of(d_llen)
+    if inprog_mode == 2 and trace_dtype_of(d_inprog) != dt:
+        raise TypeError('a per-tick in-progress trace must have the element type of the LLEN trace')
     args = ReplayArgs(ptr(d_llen), ptr(d_inprog), inprog_mode, n_ticks, n_queues, R,
-                      ptr(d_group_off), ptr(d_cur0), parr, 1, None, None, None)
+                      ptr(d_group_off), ptr(d_cur0), parr, 1, None, None, None, dt)
     off = torch.empty(R + 1, dtype=torch.int64, device=dev)
     nscratch = lib().kas_patch_events_scratch_bytes(R)
     scratch = torch.empty(max(nscratch, 8), dtype=torch.uint8, device=dev)

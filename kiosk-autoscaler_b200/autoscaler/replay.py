@@ -92,11 +92,29 @@ def _to_device_i32(x, torch, what):
     return torch.from_numpy(np.ascontiguousarray(a, dtype=np.int32)).to('cuda')
 
 
+def _to_device_trace(x, torch, what, like=None):
+    """A trace on the device: uint16 stays uint16 (half the bytes), everything else int32."""
+    if x is None:
+        return None
+    if isinstance(x, torch.Tensor):
+        if x.dtype not in (torch.int32, torch.uint16, torch.int16):
+            raise TypeError('%s must be int32 or uint16' % what)
+        return x.contiguous().to('cuda')
+    a = np.asarray(x)
+    want_u16 = a.dtype == np.uint16 if like is None else like.dtype in (torch.uint16, torch.int16)
+    if want_u16:
+        if a.size and (a.min() < 0 or a.max() > 65535):
+            raise OverflowError('%s does not fit the uint16 trace format' % what)
+        # int16 storage: same bits, universally supported by torch; the library reads uint16
+        return torch.from_numpy(np.ascontiguousarray(a, dtype=np.uint16).view(np.int16)).to('cuda')
+    return _to_device_i32(a, torch, what)
+
+
 def replay_fleet(llen, policies, inprog=None, group_off=None, cur0=None, want_totals=True,
                  want_dense=False, resource_type='deployment'):
     """Replay many resources at once.
 
-    llen       int32 [T][Q] (numpy or CUDA tensor), tick-major
+    llen       int32 or uint16 [T][Q] (numpy or CUDA tensor), tick-major
     inprog     None | [Q] | [T][Q]
     group_off  None (every queue is its own resource) | uint64 [R+1]
     cur0       None | int32 [R]
@@ -104,9 +122,12 @@ def replay_fleet(llen, policies, inprog=None, group_off=None, cur0=None, want_to
     """
     _check_type(resource_type)
     torch = engine.require_cuda()
-    d_llen = _to_device_i32(llen, torch, 'llen')
+    d_llen = _to_device_trace(llen, torch, 'llen')
     T, Q = int(d_llen.shape[0]), int(d_llen.shape[1])
-    d_ip = _to_device_i32(inprog, torch, 'inprog')
+    if inprog is not None and np.ndim(inprog) == 2:
+        d_ip = _to_device_trace(inprog, torch, 'inprog', like=d_llen)
+    else:
+        d_ip = _to_device_i32(inprog, torch, 'inprog')
     mode = 0 if d_ip is None else (1 if d_ip.dim() == 1 else 2)
     d_go = None
     R = Q
@@ -157,9 +178,12 @@ def patch_events(llen, policy, inprog=None, group_off=None, cur0=None, resource_
     for rt in types:
         _check_type(rt)
     torch = engine.require_cuda()
-    d_llen = _to_device_i32(llen, torch, 'llen')
+    d_llen = _to_device_trace(llen, torch, 'llen')
     T, Q = int(d_llen.shape[0]), int(d_llen.shape[1])
-    d_ip = _to_device_i32(inprog, torch, 'inprog')
+    if inprog is not None and np.ndim(inprog) == 2:
+        d_ip = _to_device_trace(inprog, torch, 'inprog', like=d_llen)
+    else:
+        d_ip = _to_device_i32(inprog, torch, 'inprog')
     mode = 0 if d_ip is None else (1 if d_ip.dim() == 1 else 2)
     d_go, R = None, Q
     if group_off is not None:

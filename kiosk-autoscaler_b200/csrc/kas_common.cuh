@@ -55,6 +55,36 @@ __device__ __forceinline__ int ldg_stream_i32(const void *p) {
     asm volatile("ld.global.nc.L1::no_allocate.s32 %0, [%1];" : "=r"(r) : "l"(p));
     return r;
 }
+// One element of a queue-depth trace (int32 or uint16 storage) as an int32, streaming.
+template <typename E>
+__device__ __forceinline__ int ld_trace(const E *p);
+template <>
+__device__ __forceinline__ int ld_trace<int32_t>(const int32_t *p) { return ldg_stream_i32(p); }
+template <>
+__device__ __forceinline__ int ld_trace<uint16_t>(const uint16_t *p) {
+    unsigned short r;
+    asm volatile("ld.global.nc.L1::no_allocate.u16 %0, [%1];" : "=h"(r) : "l"(p));
+    return (int)r;
+}
+// The same through the cached path (small, re-read inputs).
+template <typename E>
+__device__ __forceinline__ int ld_trace_cached(const E *p) { return (int)__ldg(p); }
+// N = 16 / sizeof(E) consecutive trace elements with one 128-bit streaming load.
+template <typename E, int N>
+__device__ __forceinline__ void ld_trace_vec(const E *p, int (&out)[N]) {
+    static_assert(N * sizeof(E) == 16, "one 128-bit load");
+    const int4 w = ldg_stream_i4(p);
+    if constexpr (sizeof(E) == 4) {
+        out[0] = w.x; out[1] = w.y; out[2] = w.z; out[3] = w.w;
+    } else {
+        const unsigned x[4] = {(unsigned)w.x, (unsigned)w.y, (unsigned)w.z, (unsigned)w.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            out[2 * k] = (int)(x[k] & 0xFFFFu);
+            out[2 * k + 1] = (int)(x[k] >> 16);
+        }
+    }
+}
 #endif
 
 }  // namespace kas

@@ -24,8 +24,8 @@ constexpr int kScanPerThread = 16;
 constexpr int kScanTile = kScanThreads * kScanPerThread;   // 4096 counts per block
 
 struct EventParams {
-    const int32_t *llen;
-    const int32_t *inprog;
+    const void *llen;       // trace elements: int32 or uint16 (template type E)
+    const void *inprog;     // per-tick term: same type; per-queue term: int32 [Q]
     const uint64_t *group_off;
     const int32_t *cur0;
     unsigned long long *event_off;   // [R+1]; counts live in [1..R] between the steps
@@ -34,11 +34,12 @@ struct EventParams {
     uint64_t Q, R;
     uint32_t T;
     int32_t inprog_mode;
+    bool u16;
     PolDev pol;
 };
 
 // One thread per resource; EMIT = false counts, EMIT = true writes.
-template <int MODE, bool EMIT>
+template <typename E, int MODE, bool EMIT>
 __global__ void __launch_bounds__(kEventThreads)
 events_kernel(const __grid_constant__ EventParams P) {
     const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -50,12 +51,14 @@ events_kernel(const __grid_constant__ EventParams P) {
     unsigned long long n = 0;
     const unsigned long long base = EMIT ? P.event_off[r] : 0ull;
     for (uint32_t t = 0; t < P.T; ++t) {
-        const int32_t *lrow = P.llen + (uint64_t)t * P.Q;
-        const int32_t *irow = P.inprog_mode == 2 ? P.inprog + (uint64_t)t * P.Q : P.inprog;
+        const E *lrow = static_cast<const E *>(P.llen) + (uint64_t)t * P.Q;
+        const E *irow = static_cast<const E *>(P.inprog) + (uint64_t)t * P.Q;          // per-tick term
+        const int32_t *iq = static_cast<const int32_t *>(P.inprog);                  // per-queue term
         long long sum = 0;
         for (uint64_t q = q0; q < q1; ++q) {
-            const int32_t l = ldg_stream_i32(lrow + q);
-            const int32_t ip = P.inprog_mode ? __ldg(irow + q) : 0;
+            const int32_t l = ld_trace<E>(lrow + q);
+            const int32_t ip = P.inprog_mode == 2 ? ld_trace<E>(irow + q)
+                                                  : (P.inprog_mode == 1 ? __ldg(iq + q) : 0);
             sum += decide<MODE>(l, ip, pol, cur);                       // autoscaler.py:255-257
         }
         const int32_t want = clip64(sum, pol.mn, pol.mx, cur);           // :259
@@ -195,8 +198,10 @@ static int fill_event_params(const kas_replay_args *a, uint32_t policy_index, Ev
     if (a->inprog_mode < 0 || a->inprog_mode > 2 || (a->inprog_mode != 0 && !a->d_inprog)) return KAS_ERR_INVALID;
     if (!a->d_group_off && a->n_resources != a->n_queues) return KAS_ERR_INVALID;
     if (a->n_resources > 0x7FFFFFFFull * kEventThreads) return KAS_ERR_UNSUPPORTED;
-    if (!aligned(a->d_llen, 4) || !aligned(a->d_inprog, 4) || !aligned(a->d_group_off, 8) ||
-        !aligned(a->d_cur0, 4))
+    if (a->trace_dtype != KAS_TRACE_INT32 && a->trace_dtype != KAS_TRACE_UINT16) return KAS_ERR_INVALID;
+    const size_t elem = a->trace_dtype == KAS_TRACE_UINT16 ? 2 : 4;
+    if (!aligned(a->d_llen, elem) || !aligned(a->d_inprog, a->inprog_mode == 2 ? elem : 4) ||
+        !aligned(a->d_group_off, 8) || !aligned(a->d_cur0, 4))
         return KAS_ERR_ALIGNMENT;
     const kas_policy &p = a->policies[policy_index];
     mode = replay_mode_for(&p, 1);
@@ -210,6 +215,7 @@ static int fill_event_params(const kas_replay_args *a, uint32_t policy_index, Ev
     P.T = a->n_ticks;
     P.inprog_mode = a->inprog_mode;
     P.pol = make_poldev(p);
+    P.u16 = a->trace_dtype == KAS_TRACE_UINT16;
     P.event_off = nullptr;
     P.events = nullptr;
     P.capacity = 0;
@@ -219,8 +225,13 @@ static int fill_event_params(const kas_replay_args *a, uint32_t policy_index, Ev
 template <bool EMIT>
 static int launch_events(const EventParams &P, int mode, cudaStream_t stream) {
     const unsigned grid = (unsigned)((P.R + kEventThreads - 1) / kEventThreads);
-    if (mode == kGeneric) events_kernel<kGeneric, EMIT><<<grid, kEventThreads, 0, stream>>>(P);
-    else events_kernel<kSimple, EMIT><<<grid, kEventThreads, 0, stream>>>(P);
+    if (P.u16) {
+        if (mode == kGeneric) events_kernel<uint16_t, kGeneric, EMIT><<<grid, kEventThreads, 0, stream>>>(P);
+        else events_kernel<uint16_t, kSimple, EMIT><<<grid, kEventThreads, 0, stream>>>(P);
+    } else {
+        if (mode == kGeneric) events_kernel<int32_t, kGeneric, EMIT><<<grid, kEventThreads, 0, stream>>>(P);
+        else events_kernel<int32_t, kSimple, EMIT><<<grid, kEventThreads, 0, stream>>>(P);
+    }
     KAS_CUDA_TRY(cudaGetLastError());
     return KAS_OK;
 }

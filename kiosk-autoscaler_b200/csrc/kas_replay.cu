@@ -24,8 +24,8 @@ constexpr int kMaxPoliciesPerLaunch = 32;
 constexpr int kTickUnroll = 4;
 
 struct ReplayParams {
-    const int32_t *llen;
-    const int32_t *inprog;
+    const void *llen;       // trace elements: int32 or uint16 (the kernels' template type E)
+    const void *inprog;     // per-tick term: same element type; per-queue term: int32 [Q]
     const uint64_t *group_off;
     const int32_t *cur0;
     kas_totals *totals;
@@ -66,7 +66,7 @@ __device__ __forceinline__ long long warp_sum_ll(long long v) {
 }
 
 // ---- every queue is its own resource (R == Q) ------------------------------
-// IPMODE 0: no in-progress term, 1: one value per queue, 2: one per (tick, queue).
+// E: storage type of the trace (int32_t or uint16_t).  IPMODE 0: no in-progress term, 1: one value per queue, 2: one per (tick, queue).
 // Blocks are numbered policy-chunk fastest, so the chunks that read the same
 // trace columns run together and share them through L2.
 #ifndef KAS_REPLAY_SWEEP_SP
@@ -78,8 +78,10 @@ __device__ __forceinline__ long long warp_sum_ll(long long v) {
 #ifndef KAS_REPLAY_MINB_SWEEP
 #define KAS_REPLAY_MINB_SWEEP 4   // the same with several policies per thread
 #endif
-template <int VEC, int SP, int IPMODE, int MODE>
-__global__ void __launch_bounds__(kReplayThreads, (SP == 1 ? KAS_REPLAY_MINB_S1 : KAS_REPLAY_MINB_SWEEP))
+template <typename E, int VEC, int SP, int IPMODE, int MODE>
+__global__ void __launch_bounds__(kReplayThreads,
+                                  (SP != 1 ? KAS_REPLAY_MINB_SWEEP
+                                           : (VEC * (IPMODE == 2 ? 2 : 1) >= 8 ? 4 : KAS_REPLAY_MINB_S1)))
 replay_identity_kernel(const __grid_constant__ ReplayParams P) {
     constexpr int U = kTickUnroll;
     const uint32_t ny = (P.pol_count + SP - 1) / SP;
@@ -108,14 +110,14 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
 #pragma unroll
     for (int v = 0; v < VEC; ++v) {
         const int32_t c0 = (valid && P.cur0) ? P.cur0[r0 + v] : 0;
-        ipq[v] = (valid && IPMODE == 1) ? P.inprog[r0 + v] : 0;
+        ipq[v] = (valid && IPMODE == 1) ? static_cast<const int32_t *>(P.inprog)[r0 + v] : 0;
 #pragma unroll
         for (int s = 0; s < SP; ++s) { cur[s][v] = c0; pt[s][v] = 0; np[s][v] = 0u; }
     }
 
     if (valid) {
-        const int32_t *lrow = P.llen + r0;
-        const int32_t *irow = IPMODE == 2 ? P.inprog + r0 : nullptr;
+        const E *lrow = static_cast<const E *>(P.llen) + r0;
+        const E *irow = IPMODE == 2 ? static_cast<const E *>(P.inprog) + r0 : nullptr;
         // one tick of VEC resources under SP policies; FASTOK: no negative input in sight
         auto step = [&](uint32_t t, const int32_t (&l)[VEC], const int32_t (&ip)[VEC], auto fastok) {
             constexpr bool FASTOK = decltype(fastok)::value;
@@ -141,10 +143,14 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
                 }
                 if (dense && live[s]) {
                     int32_t *o = P.dense + ((uint64_t)P.pol_index[pbase + s] * T + t) * P.R + r0;
-                    if constexpr (VEC == 4)
-                        *reinterpret_cast<int4 *>(o) = make_int4(cur[s][0], cur[s][1], cur[s][2], cur[s][3]);
-                    else
+                    if constexpr (VEC > 1) {
+#pragma unroll
+                        for (int j = 0; j < VEC / 4; ++j)
+                            reinterpret_cast<int4 *>(o)[j] =
+                                make_int4(cur[s][4 * j], cur[s][4 * j + 1], cur[s][4 * j + 2], cur[s][4 * j + 3]);
+                    } else {
                         o[0] = cur[s][0];
+                    }
                 }
             }
         };
@@ -154,16 +160,12 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
             for (int u = 0; u < U; ++u) {
                 const uint32_t tt = min(t + (uint32_t)u, T - 1);
                 const uint64_t o = (uint64_t)tt * Q;
-                if constexpr (VEC == 4) {
-                    const int4 a = ldg_stream_i4(lrow + o);
-                    l[u][0] = a.x; l[u][1] = a.y; l[u][2] = a.z; l[u][3] = a.w;
-                    if constexpr (IPMODE == 2) {
-                        const int4 b = ldg_stream_i4(irow + o);
-                        ip[u][0] = b.x; ip[u][1] = b.y; ip[u][2] = b.z; ip[u][3] = b.w;
-                    }
+                if constexpr (VEC > 1) {
+                    ld_trace_vec<E, VEC>(lrow + o, l[u]);
+                    if constexpr (IPMODE == 2) ld_trace_vec<E, VEC>(irow + o, ip[u]);
                 } else {
-                    l[u][0] = ldg_stream_i32(lrow + o);
-                    if constexpr (IPMODE == 2) ip[u][0] = ldg_stream_i32(irow + o);
+                    l[u][0] = ld_trace<E>(lrow + o);
+                    if constexpr (IPMODE == 2) ip[u][0] = ld_trace<E>(irow + o);
                 }
                 if constexpr (IPMODE != 2) {
 #pragma unroll
@@ -203,8 +205,8 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
             const uint64_t o = (uint64_t)t0 * Q;
 #pragma unroll
             for (int v = 0; v < VEC; ++v) {
-                l[v] = ldg_stream_i32(lrow + o + v);
-                ip[v] = IPMODE == 2 ? ldg_stream_i32(irow + o + v) : ipq[v];
+                l[v] = ld_trace<E>(lrow + o + v);
+                ip[v] = IPMODE == 2 ? ld_trace<E>(irow + o + v) : ipq[v];
             }
             step(t0, l, ip, std::false_type{});
         }
@@ -244,7 +246,7 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
 }
 
 // ---- resources that own several queues (CSR groups) ------------------------
-template <int SP, int MODE>
+template <typename E, int SP, int MODE>
 __global__ void __launch_bounds__(kReplayThreads)
 replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
     const uint32_t ny = (P.pol_count + SP - 1) / SP;
@@ -263,14 +265,16 @@ replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
         const uint64_t q0 = P.group_off ? P.group_off[r] : r;
         const uint64_t q1 = P.group_off ? P.group_off[r + 1] : r + 1;
         for (uint32_t t = 0; t < T; ++t) {
-            const int32_t *lrow = P.llen + (uint64_t)t * Q;
-            const int32_t *irow = P.inprog_mode == 2 ? P.inprog + (uint64_t)t * Q : P.inprog;
+            const E *lrow = static_cast<const E *>(P.llen) + (uint64_t)t * Q;
+            const E *irow = static_cast<const E *>(P.inprog) + (uint64_t)t * Q;      // per-tick term
+            const int32_t *iq = static_cast<const int32_t *>(P.inprog);              // per-queue term
             long long sum[SP];
 #pragma unroll
             for (int s = 0; s < SP; ++s) sum[s] = 0;
             for (uint64_t q = q0; q < q1; ++q) {
-                const int32_t l = ldg_stream_i32(lrow + q);
-                const int32_t ip = P.inprog_mode ? __ldg(irow + q) : 0;
+                const int32_t l = ld_trace<E>(lrow + q);
+                const int32_t ip = P.inprog_mode == 2 ? ld_trace<E>(irow + q)
+                                                      : (P.inprog_mode == 1 ? __ldg(iq + q) : 0);
 #pragma unroll
                 for (int s = 0; s < SP; ++s)
                     if (pbase + s < P.pol_count)
@@ -340,12 +344,14 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-template <bool TICKIP, int MODE>
+template <typename E, bool TICKIP, int MODE>
 __global__ void __launch_bounds__(32 * kSweepMaxWarps, 1)
 replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
     constexpr int SP = kSweepSP, VEC = 4;
-    extern __shared__ int4 sweep_smem[];            // [TICKIP ? 2 : 1][kSweepStages][ticks][groups][32] int4
-    constexpr int kTileVec = kSweepTileRows * 32;   // int4 per tile and array, whatever the split
+    constexpr int kEPP = 16 / (int)sizeof(E);                 // trace elements per 16-byte piece
+    constexpr int kGroupPieces = kSweepCols / kEPP;           // pieces per tick and column group
+    extern __shared__ int4 sweep_smem[];            // [TICKIP ? 2 : 1][kSweepStages][ticks][groups][kGroupPieces] int4
+    constexpr int kTileVec = kSweepTileRows * kGroupPieces;   // int4 per tile and array, whatever the split
     int4 *s_l = sweep_smem;                                  // llen tiles
     int4 *s_i = sweep_smem + kSweepStages * kTileVec;        // in-progress tiles (TICKIP only)
 
@@ -360,8 +366,8 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
     const bool valid = r0 < P.R;
     const uint32_t T = P.T;
     const uint64_t Q = P.Q;
-    const uint32_t row_vec = groups * 32u;                                   // int4 per staged tick
-    const uint32_t vec_here = (uint32_t)(min((uint64_t)groups * kSweepCols, P.R - col0) / 4);   // R % 4 == 0
+    const uint32_t row_vec = groups * kGroupPieces;                          // int4 per staged tick
+    const uint32_t vec_here = (uint32_t)(min((uint64_t)groups * kSweepCols, P.R - col0) / kEPP);   // R % kEPP == 0
 
     PolDev pol[SP];
     bool live[SP];
@@ -380,7 +386,7 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
 #pragma unroll
     for (int v = 0; v < VEC; ++v) {
         const int32_t c0 = (valid && P.cur0) ? P.cur0[r0 + v] : 0;
-        ipq[v] = (valid && P.inprog_mode == 1) ? P.inprog[r0 + v] : 0;
+        ipq[v] = (valid && P.inprog_mode == 1) ? static_cast<const int32_t *>(P.inprog)[r0 + v] : 0;
 #pragma unroll
         for (int s = 0; s < SP; ++s) { cur[s][v] = c0; pt[s][v] = 0; np[s][v] = 0u; }
     }
@@ -396,9 +402,9 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
             for (uint32_t e = threadIdx.x; e < nt * row_vec; e += blockDim.x) {
                 const uint32_t t = e / row_vec, c = e - t * row_vec;
                 if (c < vec_here) {
-                    const uint64_t g = (uint64_t)(t0 + t) * Q + col0 + 4ull * c;
-                    cp_async_16(dl + e, P.llen + g);
-                    if (TICKIP) cp_async_16(di + e, P.inprog + g);
+                    const uint64_t g = (uint64_t)(t0 + t) * Q + col0 + (uint64_t)kEPP * c;
+                    cp_async_16(dl + e, static_cast<const E *>(P.llen) + g);
+                    if (TICKIP) cp_async_16(di + e, static_cast<const E *>(P.inprog) + g);
                 }
             }
         }
@@ -412,9 +418,22 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
         stage(k + 2);                  // refill the buffer tile k-1 occupied
         const uint32_t t0 = k * tile_ticks;
         const uint32_t nt = min(tile_ticks, T - t0);
-        const int4 *tl = s_l + (k % kSweepStages) * kTileVec + cg * 32u + lane;
-        const int4 *ti = s_i + (k % kSweepStages) * kTileVec + cg * 32u + lane;
+        // this lane's four elements of a staged tick: element (cg * 128 + 4 * lane) of the row
+        const E *tl = reinterpret_cast<const E *>(s_l + (k % kSweepStages) * kTileVec) + cg * kSweepCols + 4u * lane;
+        const E *ti = reinterpret_cast<const E *>(s_i + (k % kSweepStages) * kTileVec) + cg * kSweepCols + 4u * lane;
+        const uint32_t row_elems = row_vec * kEPP;
         if (valid && (live[0] || live[SP - 1])) {
+            // four consecutive elements out of shared memory (one 128- or 64-bit load)
+            auto read4 = [](const E *p, int32_t (&o)[VEC]) {
+                if constexpr (sizeof(E) == 4) {
+                    const int4 a = *reinterpret_cast<const int4 *>(p);
+                    o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w;
+                } else {
+                    const uint2 a = *reinterpret_cast<const uint2 *>(p);
+                    o[0] = (int32_t)(a.x & 0xFFFFu); o[1] = (int32_t)(a.x >> 16);
+                    o[2] = (int32_t)(a.y & 0xFFFFu); o[3] = (int32_t)(a.y >> 16);
+                }
+            };
             // G ticks at a time: their rows are read from shared memory first, one sign
             // test picks the arithmetic for all of them, then the recurrences run
             auto ticks = [&](uint32_t t, auto gtag) {
@@ -423,11 +442,9 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
                 int32_t any = 0;
 #pragma unroll
                 for (int g = 0; g < G; ++g) {
-                    const int4 a = tl[(t + g) * row_vec];
-                    l[g][0] = a.x; l[g][1] = a.y; l[g][2] = a.z; l[g][3] = a.w;
+                    read4(tl + (t + g) * row_elems, l[g]);
                     if (TICKIP) {
-                        const int4 b = ti[(t + g) * row_vec];
-                        ip[g][0] = b.x; ip[g][1] = b.y; ip[g][2] = b.z; ip[g][3] = b.w;
+                        read4(ti + (t + g) * row_elems, ip[g]);
                     } else {
 #pragma unroll
                         for (int v = 0; v < VEC; ++v) ip[g][v] = ipq[v];
@@ -528,7 +545,7 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
 constexpr int kSmallTileElems = 2048;      // trace elements per tile and warp (8 KB, twice with a per-tick in-progress trace)
 constexpr uint64_t kSmallMaxResources = 4096;
 
-template <int MODE>
+template <typename E, int MODE>
 __global__ void __launch_bounds__(32)
 replay_small_kernel(const __grid_constant__ ReplayParams P) {
     __shared__ int32_t s_l[kSmallTileElems];
@@ -551,9 +568,9 @@ replay_small_kernel(const __grid_constant__ ReplayParams P) {
         for (uint32_t e = lane; e < elems; e += 32) {
             const uint32_t t = e / nq, j = e - t * nq;
             const uint64_t g = (uint64_t)(t0 + t) * P.Q + q0 + j;
-            s_l[e] = ldg_stream_i32(P.llen + g);
-            s_i[e] = P.inprog_mode == 2 ? ldg_stream_i32(P.inprog + g)
-                                        : (P.inprog_mode == 1 ? __ldg(P.inprog + q0 + j) : 0);
+            s_l[e] = ld_trace<E>(static_cast<const E *>(P.llen) + g);
+            s_i[e] = P.inprog_mode == 2 ? ld_trace<E>(static_cast<const E *>(P.inprog) + g)
+                                        : (P.inprog_mode == 1 ? __ldg(static_cast<const int32_t *>(P.inprog) + q0 + j) : 0);
         }
         __syncwarp();
         if (live) {
@@ -647,7 +664,7 @@ synth_trace_kernel(uint64_t seed, uint32_t T, uint64_t q_first, uint64_t n_q, in
     }
 }
 
-template <int VEC, int SP>
+template <typename E, int VEC, int SP>
 static void launch_identity(const ReplayParams &P, int mode, cudaStream_t stream) {
     const uint64_t threads = (P.R + VEC - 1) / VEC;
     const uint64_t nx = (threads + kReplayThreads - 1) / kReplayThreads;
@@ -655,9 +672,9 @@ static void launch_identity(const ReplayParams &P, int mode, cudaStream_t stream
     const unsigned grid = (unsigned)(nx * ny);
 #define KAS_LAUNCH_ID(IPM)                                                                        \
     do {                                                                                          \
-        if (mode == kSimpleK1) replay_identity_kernel<VEC, SP, IPM, kSimpleK1><<<grid, kReplayThreads, 0, stream>>>(P); \
-        else if (mode == kSimple) replay_identity_kernel<VEC, SP, IPM, kSimple><<<grid, kReplayThreads, 0, stream>>>(P); \
-        else replay_identity_kernel<VEC, SP, IPM, kGeneric><<<grid, kReplayThreads, 0, stream>>>(P);     \
+        if (mode == kSimpleK1) replay_identity_kernel<E, VEC, SP, IPM, kSimpleK1><<<grid, kReplayThreads, 0, stream>>>(P); \
+        else if (mode == kSimple) replay_identity_kernel<E, VEC, SP, IPM, kSimple><<<grid, kReplayThreads, 0, stream>>>(P); \
+        else replay_identity_kernel<E, VEC, SP, IPM, kGeneric><<<grid, kReplayThreads, 0, stream>>>(P);     \
     } while (0)
     if (P.inprog_mode == 0) KAS_LAUNCH_ID(0);
     else if (P.inprog_mode == 1) KAS_LAUNCH_ID(1);
@@ -665,6 +682,7 @@ static void launch_identity(const ReplayParams &P, int mode, cudaStream_t stream
 #undef KAS_LAUNCH_ID
 }
 
+template <typename E>
 static int launch_sweep(const ReplayParams &P, int mode, cudaStream_t stream) {
     const bool tickip = P.inprog_mode == 2;
     const unsigned chunks = (P.pol_count + kSweepSP - 1) / kSweepSP;          // <= 16
@@ -672,10 +690,10 @@ static int launch_sweep(const ReplayParams &P, int mode, cudaStream_t stream) {
     const unsigned warps = chunks * groups;
     const uint64_t cols_per_block = (uint64_t)groups * kSweepCols;
     const unsigned grid = (unsigned)((P.R + cols_per_block - 1) / cols_per_block);
-    const size_t smem = (size_t)(tickip ? 2 : 1) * kSweepStages * kSweepTileRows * 32 * sizeof(int4);
+    const size_t smem = (size_t)(tickip ? 2 : 1) * kSweepStages * kSweepTileRows * kSweepCols * sizeof(E);
 #define KAS_LAUNCH_SWEEP(TI, MD)                                                                   \
     do {                                                                                           \
-        auto kern = replay_sweep_kernel<TI, MD>;                                                   \
+        auto kern = replay_sweep_kernel<E, TI, MD>;                                                   \
         if (smem > 48 * 1024)                                                                      \
             KAS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
                                               (int)smem));                                         \
@@ -690,52 +708,34 @@ static int launch_sweep(const ReplayParams &P, int mode, cudaStream_t stream) {
     return KAS_OK;
 }
 
+template <typename E>
 static void launch_small(const ReplayParams &P, int mode, cudaStream_t stream) {
-    if (mode != kGeneric) replay_small_kernel<kSimple><<<(unsigned)P.R, 32, 0, stream>>>(P);
-    else replay_small_kernel<kGeneric><<<(unsigned)P.R, 32, 0, stream>>>(P);
+    if (mode != kGeneric) replay_small_kernel<E, kSimple><<<(unsigned)P.R, 32, 0, stream>>>(P);
+    else replay_small_kernel<E, kGeneric><<<(unsigned)P.R, 32, 0, stream>>>(P);
 }
 
-template <int SP>
+template <typename E, int SP>
 static void launch_grouped(const ReplayParams &P, int mode, cudaStream_t stream) {
     const uint64_t nx = (P.R + kReplayThreads - 1) / kReplayThreads;
     const uint32_t ny = (P.pol_count + SP - 1) / SP;
     const unsigned grid = (unsigned)(nx * ny);
-    if (mode != kGeneric) replay_grouped_kernel<SP, kSimple><<<grid, kReplayThreads, 0, stream>>>(P);
-    else replay_grouped_kernel<SP, kGeneric><<<grid, kReplayThreads, 0, stream>>>(P);
+    if (mode != kGeneric) replay_grouped_kernel<E, SP, kSimple><<<grid, kReplayThreads, 0, stream>>>(P);
+    else replay_grouped_kernel<E, SP, kGeneric><<<grid, kReplayThreads, 0, stream>>>(P);
 }
 
 }  // namespace kas
 
 using namespace kas;
 
-extern "C" {
-
-int kas_replay(const kas_replay_args *a, void *stream_v) {
-    if (!a || !a->policies || a->n_policies == 0) return KAS_ERR_INVALID;
-    if (a->n_queues == 0 || a->n_resources == 0) return KAS_ERR_INVALID;
-    if (a->n_ticks && !a->d_llen) return KAS_ERR_INVALID;
-    if (a->inprog_mode < 0 || a->inprog_mode > 2) return KAS_ERR_INVALID;
-    if (a->inprog_mode != 0 && !a->d_inprog) return KAS_ERR_INVALID;
-    if (!a->d_group_off && a->n_resources != a->n_queues) return KAS_ERR_INVALID;
-    if (!a->d_totals && !a->d_sums && !a->d_dense) return KAS_ERR_INVALID;
-    if (a->n_resources > (0x7FFFFFFFull / kMaxPoliciesPerLaunch) * kReplayThreads) return KAS_ERR_UNSUPPORTED;
-    if (!aligned(a->d_llen, 4) || !aligned(a->d_inprog, 4) || !aligned(a->d_dense, 4) ||
-        !aligned(a->d_totals, 8) || !aligned(a->d_sums, 8) || !aligned(a->d_group_off, 8) ||
-        !aligned(a->d_cur0, 4))
-        return KAS_ERR_ALIGNMENT;
-    const int mode = replay_mode_for(a->policies, a->n_policies);
-    if (mode < 0) return KAS_ERR_ZERO_DIVISION;
-    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
-    if (a->d_sums)
-        KAS_CUDA_TRY(cudaMemsetAsync(a->d_sums, 0, sizeof(int64_t) * 3 * a->n_policies, stream));
-
+// Everything after argument checking, for one element type of the trace.
+template <typename E>
+static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream) {
+    constexpr int kVec = 16 / (int)sizeof(E);                 // elements per 128-bit load: 4 or 8
     const bool identity = a->d_group_off == nullptr;
     const bool tickip = a->inprog_mode == 2;
-    if (a->n_ticks == 0) return KAS_ERR_INVALID;
-    const bool vec4 = identity && (a->n_queues % 4 == 0) && aligned(a->d_llen, 16) &&
-                      (!tickip || aligned(a->d_inprog, 16)) &&
-                      (a->inprog_mode != 1 || aligned(a->d_inprog, 4)) &&
-                      (!a->d_dense || aligned(a->d_dense, 16)) && a->n_resources >= 4096;
+    const bool vec = identity && (a->n_queues % kVec == 0) && aligned(a->d_llen, 16) &&
+                     (!tickip || aligned(a->d_inprog, 16)) &&
+                     (!a->d_dense || aligned(a->d_dense, 16)) && a->n_resources >= 4096;
 
     // few resources: a warp per resource with its queues staged in shared memory
     // (needs every resource's queues of one tick to fit a tile)
@@ -747,12 +747,11 @@ int kas_replay(const kas_replay_args *a, void *stream_v) {
     // the caller's indices either way.
     std::vector<uint32_t> order(a->n_policies);
     for (uint32_t i = 0; i < a->n_policies; ++i) order[i] = i;
-    const bool sweep_path = !small && identity && vec4 && a->n_policies > 1;
+    const bool sweep_path = !small && identity && vec && a->n_policies > 1;
     if (sweep_path)
         std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) {
             return a->policies[x].keys_per_pod < a->policies[y].keys_per_pod;
         });
-    if (a->n_policies > 65535) return KAS_ERR_UNSUPPORTED;
     for (uint32_t first = 0; first < a->n_policies; first += kMaxPoliciesPerLaunch) {
         ReplayParams P;
         P.llen = a->d_llen;
@@ -782,26 +781,52 @@ int kas_replay(const kas_replay_args *a, void *stream_v) {
             P.pol_index[s] = (uint16_t)idx;
         }
         if (small) {
-            launch_small(P, mode, stream);
+            launch_small<E>(P, mode, stream);
         } else if (identity) {
             if (P.pol_count == 1) {
-                if (vec4) launch_identity<4, 1>(P, mode, stream);
-                else launch_identity<1, 1>(P, mode, stream);
+                if (vec) launch_identity<E, kVec, 1>(P, mode, stream);
+                else launch_identity<E, 1, 1>(P, mode, stream);
             } else {
-                if (vec4) {
-                    const int st = launch_sweep(P, mode, stream);
+                if (vec) {
+                    const int st = launch_sweep<E>(P, mode, stream);
                     if (st != KAS_OK) return st;
                 } else {
-                    launch_identity<1, 4>(P, mode, stream);
+                    launch_identity<E, 1, 4>(P, mode, stream);
                 }
             }
         } else {
-            if (P.pol_count == 1) launch_grouped<1>(P, mode, stream);
-            else launch_grouped<4>(P, mode, stream);
+            if (P.pol_count == 1) launch_grouped<E, 1>(P, mode, stream);
+            else launch_grouped<E, 4>(P, mode, stream);
         }
         KAS_CUDA_TRY(cudaGetLastError());
     }
     return KAS_OK;
+}
+
+extern "C" {
+
+
+int kas_replay(const kas_replay_args *a, void *stream_v) {
+    if (!a || !a->policies || a->n_policies == 0 || a->n_policies > 65535) return KAS_ERR_INVALID;
+    if (a->n_queues == 0 || a->n_resources == 0 || a->n_ticks == 0 || !a->d_llen) return KAS_ERR_INVALID;
+    if (a->inprog_mode < 0 || a->inprog_mode > 2) return KAS_ERR_INVALID;
+    if (a->inprog_mode != 0 && !a->d_inprog) return KAS_ERR_INVALID;
+    if (a->trace_dtype != KAS_TRACE_INT32 && a->trace_dtype != KAS_TRACE_UINT16) return KAS_ERR_INVALID;
+    if (!a->d_group_off && a->n_resources != a->n_queues) return KAS_ERR_INVALID;
+    if (!a->d_totals && !a->d_sums && !a->d_dense) return KAS_ERR_INVALID;
+    if (a->n_resources > (0x7FFFFFFFull / kMaxPoliciesPerLaunch) * kReplayThreads) return KAS_ERR_UNSUPPORTED;
+    const size_t elem = a->trace_dtype == KAS_TRACE_UINT16 ? 2 : 4;
+    if (!aligned(a->d_llen, elem) || !aligned(a->d_inprog, a->inprog_mode == 2 ? elem : 4) ||
+        !aligned(a->d_dense, 4) || !aligned(a->d_totals, 8) || !aligned(a->d_sums, 8) ||
+        !aligned(a->d_group_off, 8) || !aligned(a->d_cur0, 4))
+        return KAS_ERR_ALIGNMENT;
+    const int mode = replay_mode_for(a->policies, a->n_policies);
+    if (mode < 0) return KAS_ERR_ZERO_DIVISION;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    if (a->d_sums)
+        KAS_CUDA_TRY(cudaMemsetAsync(a->d_sums, 0, sizeof(int64_t) * 3 * a->n_policies, stream));
+    return a->trace_dtype == KAS_TRACE_UINT16 ? replay_typed<uint16_t>(a, mode, stream)
+                                              : replay_typed<int32_t>(a, mode, stream);
 }
 
 int kas_decide(const int64_t *d_a, const int64_t *d_kpp, const int64_t *d_mn, const int64_t *d_mx,

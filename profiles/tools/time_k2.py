@@ -12,6 +12,8 @@ from autoscaler import engine  # noqa: E402
 T = int(os.environ.get('KAS_BENCH_REPLAY_T', 2000))
 Q = int(os.environ.get('KAS_BENCH_REPLAY_Q', 1_000_000))
 trace = engine.synth_trace(3, T, 0, Q)
+if os.environ.get('KAS_TRACE_DTYPE', 'int32') == 'uint16':
+    trace = trace.to(torch.int16)      # values < 800: same bits as uint16
 
 
 def timed(pol, reps):
@@ -29,6 +31,6 @@ def timed(pol, reps):
 
 m1, o1 = timed([(1, 0, 1)], 10)
 ms, os_ = timed(bench.SWEEP, 3)
-print('%-28s S=1 %.3f ms (%.0f GB/s)  sweep41 %.2f ms (%.3e dec/s)  chk=%d/%d' % (
-    os.path.basename(engine.LIB_PATH), m1, T * Q * 4 / m1 / 1e6, ms, T * Q * 41 / ms * 1e3,
+print('%-28s ' % os.environ.get('KAS_TRACE_DTYPE', 'int32') + ' S=1 %.3f ms (%.0f GB/s of int32-equivalent)  sweep41 %.2f ms (%.3e dec/s)  chk=%d/%d' % (
+    m1, T * Q * 4 / m1 / 1e6, ms, T * Q * 41 / ms * 1e3,
     int(o1['sums'][0, 0]), int(os_['sums'][:, 0].sum())), flush=True)

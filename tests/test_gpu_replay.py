@@ -205,3 +205,36 @@ def test_patch_events_match_reference_fixture():
                                              resource_types=case['type'])
         field = 'replicas' if case['type'] == 'deployment' else 'parallelism'
         assert [b['spec'][field] for _, b in log.bodies(0)] == case['patches']
+
+
+@pytest.mark.parametrize('shape', ['vec8', 'scalar', 'grouped', 'small'])
+@pytest.mark.parametrize('pol', ['one', 'sweep', 'negative'])
+@pytest.mark.parametrize('ipmode', [0, 1, 2])
+def test_uint16_trace_format(shape, pol, ipmode):
+    """The uint16 storage of the trace (half the bytes) gives the same integers."""
+    import autoscaler
+    from oracle import coracle
+    rng = np.random.default_rng(hash(('u16', pol, shape, ipmode)) % (2 ** 32))
+    T, Q = {'vec8': (45, 8192), 'scalar': (33, 4100), 'grouped': (29, 5000), 'small': (150, 40)}[shape]
+    llen = rng.integers(0, 60, size=(T, Q)).astype(np.uint16)
+    llen[rng.random((T, Q)) < 0.5] = 0
+    llen[rng.random((T, Q)) < 0.01] = 65535
+    go = None
+    if shape == 'grouped':
+        _, go = helpers.random_fleet(rng, 1, Q, grouped=True)
+    inprog = None
+    if ipmode == 1:
+        inprog = rng.integers(-3 if pol == 'negative' else 0, 5, size=Q).astype(np.int32)
+    elif ipmode == 2:
+        inprog = rng.integers(0, 9, size=(T, Q)).astype(np.uint16)
+    R = Q if go is None else len(go) - 1
+    cur0 = rng.integers(0, 12, size=R).astype(np.int32)
+    want = coracle.replay(llen.astype(np.int32), None if inprog is None else inprog.astype(np.int32), go,
+                          cur0, POLICY_SETS[pol], want_dense=True)
+    got = autoscaler.replay.replay_fleet(llen, POLICY_SETS[pol], inprog=inprog, group_off=go, cur0=cur0,
+                                         want_dense=True)
+    assert (got.dense == want['dense']).all()
+    assert (got.pod_ticks == want['pod_ticks']).all() and (got.n_patches == want['n_patches']).all()
+    assert (got.sums[:, 0] == want['pod_ticks'].sum(0)).all()
+    log = autoscaler.replay.patch_events(llen, POLICY_SETS[pol][0], inprog=inprog, group_off=go, cur0=cur0)
+    assert (np.diff(log.off.astype(np.int64)) == want['n_patches'][:, 0]).all()
