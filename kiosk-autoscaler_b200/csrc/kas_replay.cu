@@ -323,9 +323,9 @@ replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
 
 // ---- policy sweeps over single-queue resources: the trace is read ONCE ---------
 // Under a sweep every policy needs the same trace element.  A block owns a run of
-// adjacent resources and ALL policies of the launch: its threads stage tiles of the
-// trace in shared memory with asynchronous copies (cp.async, three tile buffers, one
-// block barrier per tile) and every warp replays the tile for two policies and 128
+// adjacent resources and ALL policies of the launch: tiles of the trace are staged in
+// shared memory by TMA bulk copies landing on an mbarrier per stage (three tile
+// buffers, one block barrier per tile) and every warp replays the tile for two policies and 128
 // resources out of shared memory.  DRAM traffic is the trace itself, whatever the
 // number of policies; the kernel is then bound by the integer pipes alone.
 // A block always has about 16 warps (4 per scheduler): with C policy pairs it covers
@@ -343,6 +343,30 @@ __device__ __forceinline__ void cp_async_16(void *smem_dst, const void *gmem_src
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+#ifndef KAS_SWEEP_TMA
+#define KAS_SWEEP_TMA 1   // stage tiles with bulk asynchronous copies (TMA, cp.async.bulk + mbarrier); 0: cp.async
+#endif
+// mbarrier + 1-D bulk copy (global -> shared), the sm_90+/sm_100 TMA path for contiguous runs
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    const uint32_t a = (uint32_t)__cvta_generic_to_shared(bar);
+    uint32_t done = 0;
+    while (!done) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(a), "r"(parity) : "memory");
+    }
+}
+__device__ __forceinline__ void bulk_copy_g2s(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src), "r"(bytes),
+                   "r"((uint32_t)__cvta_generic_to_shared(bar)) : "memory");
+}
 
 template <typename E, bool TICKIP, int MODE>
 __global__ void __launch_bounds__(32 * kSweepMaxWarps, 1)
@@ -391,8 +415,43 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
         for (int s = 0; s < SP; ++s) { cur[s][v] = c0; pt[s][v] = 0; np[s][v] = 0u; }
     }
 
-    // stage tile `k` into buffer k % kSweepStages: every thread copies 16-byte pieces
     const uint32_t n_tiles = (T + tile_ticks - 1) / tile_ticks;
+#if KAS_SWEEP_TMA
+    // stage tile `k` into buffer k % kSweepStages: one thread issues a bulk copy per
+    // tick (the block's columns of a tick are one contiguous run) and the bytes land
+    // on the stage's mbarrier; everybody waits on that barrier's phase
+    __shared__ uint64_t bars[kSweepStages];
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int i = 0; i < kSweepStages; ++i) mbar_init(&bars[i], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const uint32_t row_bytes_here = vec_here * 16u;
+    auto stage = [&](uint32_t k) {
+        if (threadIdx.x == 0 && k < n_tiles) {
+            const uint32_t t0 = k * tile_ticks;
+            const uint32_t nt = min(tile_ticks, T - t0);
+            uint64_t *bar = &bars[k % kSweepStages];
+            int4 *dl = s_l + (k % kSweepStages) * kTileVec;
+            int4 *di = s_i + (k % kSweepStages) * kTileVec;
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // earlier reads of this buffer are done
+            mbar_expect_tx(bar, nt * row_bytes_here * (TICKIP ? 2u : 1u));
+            for (uint32_t t = 0; t < nt; ++t) {
+                const uint64_t g = (uint64_t)(t0 + t) * Q + col0;
+                bulk_copy_g2s(dl + t * row_vec, static_cast<const E *>(P.llen) + g, row_bytes_here, bar);
+                if (TICKIP) bulk_copy_g2s(di + t * row_vec, static_cast<const E *>(P.inprog) + g, row_bytes_here, bar);
+            }
+        }
+    };
+    stage(0);
+    stage(1);
+    for (uint32_t k = 0; k < n_tiles; ++k) {
+        mbar_wait(&bars[k % kSweepStages], (k / kSweepStages) & 1u);   // tile k has landed
+        __syncthreads();               // all are done with tile k-1
+        stage(k + 2);                  // refill the buffer tile k-1 occupied
+#else
+    // stage tile `k` into buffer k % kSweepStages: every thread copies 16-byte pieces
     auto stage = [&](uint32_t k) {
         if (k < n_tiles) {
             const uint32_t t0 = k * tile_ticks;
@@ -416,6 +475,7 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
         cp_async_wait<1>();            // this thread's pieces of tile k have landed
         __syncthreads();               // ... and everybody else's; all are done with tile k-1
         stage(k + 2);                  // refill the buffer tile k-1 occupied
+#endif
         const uint32_t t0 = k * tile_ticks;
         const uint32_t nt = min(tile_ticks, T - t0);
         // this lane's four elements of a staged tick: element (cg * 128 + 4 * lane) of the row
@@ -500,7 +560,9 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
             for (; t < nt; ++t) ticks(t, std::integral_constant<int, 1>{});
         }
     }
+#if !KAS_SWEEP_TMA
     cp_async_wait<0>();
+#endif
 
     if (valid && P.totals) {
 #pragma unroll
@@ -694,9 +756,9 @@ static int launch_sweep(const ReplayParams &P, int mode, cudaStream_t stream) {
 #define KAS_LAUNCH_SWEEP(TI, MD)                                                                   \
     do {                                                                                           \
         auto kern = replay_sweep_kernel<E, TI, MD>;                                                   \
-        if (smem > 48 * 1024)                                                                      \
-            KAS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
-                                              (int)smem));                                         \
+        /* dynamic tiles + the static mbarriers can pass the 48 KB default */                      \
+        KAS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
+                                          (int)smem));                                             \
         kern<<<grid, 32 * warps, smem, stream>>>(P);                                               \
     } while (0)
     if (mode != kGeneric) {
