@@ -216,6 +216,10 @@ typedef struct kas_replay_args {
                                    allreduce carries), or NULL                     */
     int32_t *d_dense;           /* [S][T][R] replicas after each tick, or NULL     */
     int32_t trace_dtype;        /* KAS_TRACE_INT32 (0) or KAS_TRACE_UINT16          */
+    const uint8_t *d_patch_fail;/* [T][R] or NULL: non-zero = the patch call of that
+                                   tick and resource raises ApiException, which
+                                   scale() logs and swallows (autoscaler.py:267-273):
+                                   the call counts in n_patches, the replicas stay   */
 } kas_replay_args;
 
 /* Domain: trace values and cur0 any int32; policies any int32 with

@@ -110,8 +110,17 @@ def _to_device_trace(x, torch, what, like=None):
     return _to_device_i32(a, torch, what)
 
 
+def _to_device_fail(patch_fail, torch, T, R):
+    if patch_fail is None:
+        return None
+    a = np.ascontiguousarray(np.asarray(patch_fail) != 0, dtype=np.uint8)
+    if a.shape != (T, R):
+        raise ValueError('patch_fail must be [T][R] = [%d][%d]' % (T, R))
+    return torch.from_numpy(a).to('cuda')
+
+
 def replay_fleet(llen, policies, inprog=None, group_off=None, cur0=None, want_totals=True,
-                 want_dense=False, resource_type='deployment'):
+                 want_dense=False, resource_type='deployment', patch_fail=None):
     """Replay many resources at once.
 
     llen       int32 or uint16 [T][Q] (numpy or CUDA tensor), tick-major
@@ -119,6 +128,9 @@ def replay_fleet(llen, policies, inprog=None, group_off=None, cur0=None, want_to
     group_off  None (every queue is its own resource) | uint64 [R+1]
     cur0       None | int32 [R]
     policies   sequence of (keys_per_pod, min_pods, max_pods)
+    patch_fail None | bool [T][R]: the patch call of that tick and resource raises
+               ApiException, which ``scale`` swallows (autoscaler.py:267-273 of the
+               reference): the call counts, the replicas stay
     """
     _check_type(resource_type)
     torch = engine.require_cuda()
@@ -140,7 +152,7 @@ def replay_fleet(llen, policies, inprog=None, group_off=None, cur0=None, want_to
     d_c0 = _to_device_i32(cur0, torch, 'cur0')
     out = engine.replay(d_llen, T, Q, policies, d_inprog=d_ip, inprog_mode=mode, d_group_off=d_go,
                         n_resources=R, d_cur0=d_c0, want_totals=want_totals, want_sums=True,
-                        want_dense=want_dense)
+                        want_dense=want_dense, d_patch_fail=_to_device_fail(patch_fail, torch, T, R))
     res = ReplayResult(policies,
                        totals=engine.totals_to_host(out['totals']) if want_totals else None,
                        sums=out['sums'].cpu().numpy(),
@@ -170,7 +182,8 @@ class PatchLog(object):
         return [(int(e['tick']), {'spec': {field: int(e['to_pods'])}}) for e in self.of(r)]
 
 
-def patch_events(llen, policy, inprog=None, group_off=None, cur0=None, resource_types='deployment'):
+def patch_events(llen, policy, inprog=None, group_off=None, cur0=None, resource_types='deployment',
+                 patch_fail=None):
     """Patch-event stream of ONE policy over a fleet (same inputs as replay_fleet).
     ``resource_types`` is one type for all resources or a sequence with one
     entry per resource ('deployment' / 'job'); it only selects the body field."""
@@ -196,12 +209,14 @@ def patch_events(llen, policy, inprog=None, group_off=None, cur0=None, resource_
         raise ValueError('resource_types must have one entry per resource')
     d_c0 = _to_device_i32(cur0, torch, 'cur0')
     off, ev = engine.patch_events(d_llen, T, Q, policy, d_inprog=d_ip, inprog_mode=mode,
-                                  d_group_off=d_go, n_resources=R, d_cur0=d_c0)
+                                  d_group_off=d_go, n_resources=R, d_cur0=d_c0,
+                                  d_patch_fail=_to_device_fail(patch_fail, torch, T, R))
     return PatchLog(off, ev, resource_types)
 
 
 def replay_one(queue_names, llen_trace, policies, inprog=None, current_pods=0,
-               resource_type='deployment', managed=('deployment', 'job'), want_dense=False):
+               resource_type='deployment', managed=('deployment', 'job'), want_dense=False,
+               patch_fail=None):
     """One resource fed by ``len(queue_names)`` queues (what one reference pod
     manages): llen_trace [T][Q] in the order of ``queue_names``."""
     _check_type(resource_type, managed)
@@ -211,7 +226,8 @@ def replay_one(queue_names, llen_trace, policies, inprog=None, current_pods=0,
     return replay_fleet(a, policies, inprog=inprog,
                         group_off=np.array([0, len(queue_names)], dtype=np.uint64),
                         cur0=np.array([current_pods], dtype=np.int64), want_dense=want_dense,
-                        resource_type=resource_type)
+                        resource_type=resource_type,
+                        patch_fail=None if patch_fail is None else np.asarray(patch_fail).reshape(-1, 1))
 
 
 # --------------------------------------------------------------------------

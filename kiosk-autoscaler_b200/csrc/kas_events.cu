@@ -28,6 +28,7 @@ struct EventParams {
     const void *inprog;     // per-tick term: same type; per-queue term: int32 [Q]
     const uint64_t *group_off;
     const int32_t *cur0;
+    const uint8_t *patch_fail;       // [T][R] or null
     unsigned long long *event_off;   // [R+1]; counts live in [1..R] between the steps
     kas_patch_event *events;
     uint64_t capacity;
@@ -71,7 +72,7 @@ events_kernel(const __grid_constant__ EventParams P) {
                 P.events[base + n] = e;
             }
             ++n;
-            cur = want;
+            if (!(P.patch_fail && P.patch_fail[(uint64_t)t * P.R + r])) cur = want;    // :267-273
         }
     }
     if (!EMIT) {
@@ -210,6 +211,7 @@ static int fill_event_params(const kas_replay_args *a, uint32_t policy_index, Ev
     P.inprog = a->d_inprog;
     P.group_off = a->d_group_off;
     P.cur0 = a->d_cur0;
+    P.patch_fail = a->d_patch_fail;
     P.Q = a->n_queues;
     P.R = a->n_resources;
     P.T = a->n_ticks;

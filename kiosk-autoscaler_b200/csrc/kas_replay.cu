@@ -28,6 +28,7 @@ struct ReplayParams {
     const void *inprog;     // per-tick term: same element type; per-queue term: int32 [Q]
     const uint64_t *group_off;
     const int32_t *cur0;
+    const uint8_t *patch_fail;   // [T][R] or null: the patch call of (tick, resource) raises and is swallowed
     kas_totals *totals;
     unsigned long long *sums;
     int32_t *dense;
@@ -268,6 +269,7 @@ replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
             const E *lrow = static_cast<const E *>(P.llen) + (uint64_t)t * Q;
             const E *irow = static_cast<const E *>(P.inprog) + (uint64_t)t * Q;      // per-tick term
             const int32_t *iq = static_cast<const int32_t *>(P.inprog);              // per-queue term
+            const bool failed = P.patch_fail && P.patch_fail[(uint64_t)t * P.R + r];
             long long sum[SP];
 #pragma unroll
             for (int s = 0; s < SP; ++s) sum[s] = 0;
@@ -285,10 +287,12 @@ replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
                 if (pbase + s < P.pol_count) {
                     const PolDev &p = P.pol[pbase + s];
                     const int32_t want = clip64(sum[s], p.mn, p.mx, cur[s]);          // :259
-                    np[s] += (want != cur[s]);
-                    cur[s] = want;
-                    pt[s] += want;
-                    if (P.dense) P.dense[((uint64_t)P.pol_index[pbase + s] * T + t) * P.R + r] = want;
+                    if (want != cur[s]) {                                             // :227
+                        np[s] += 1;                                                   // the patch call is made
+                        if (!failed) cur[s] = want;                                   // raised and swallowed: :267-273
+                    }
+                    pt[s] += cur[s];
+                    if (P.dense) P.dense[((uint64_t)P.pol_index[pbase + s] * T + t) * P.R + r] = cur[s];
                 }
             }
         }
@@ -641,10 +645,12 @@ replay_small_kernel(const __grid_constant__ ReplayParams P) {
                 for (uint32_t j = 0; j < nq; ++j)
                     sum += decide<MODE>(s_l[t * nq + j], s_i[t * nq + j], pol, cur);      // :255-257
                 const int32_t want = clip64(sum, pol.mn, pol.mx, cur);                    // :259
-                np += (want != cur);                                                      // :227
-                cur = want;
-                pt += want;
-                if (P.dense) P.dense[((uint64_t)P.pol_index[lane] * T + t0 + t) * P.R + r] = want;
+                if (want != cur) {                                                        // :227
+                    np += 1;                                                              // the patch call is made
+                    if (!(P.patch_fail && P.patch_fail[(uint64_t)(t0 + t) * P.R + r])) cur = want;   // :267-273
+                }
+                pt += cur;
+                if (P.dense) P.dense[((uint64_t)P.pol_index[lane] * T + t0 + t) * P.R + r] = cur;
             }
         }
     }
@@ -809,7 +815,7 @@ static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream)
     // the caller's indices either way.
     std::vector<uint32_t> order(a->n_policies);
     for (uint32_t i = 0; i < a->n_policies; ++i) order[i] = i;
-    const bool sweep_path = !small && identity && vec && a->n_policies > 1;
+    const bool sweep_path = !small && identity && vec && a->n_policies > 1 && !a->d_patch_fail;
     if (sweep_path)
         std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) {
             return a->policies[x].keys_per_pod < a->policies[y].keys_per_pod;
@@ -820,6 +826,7 @@ static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream)
         P.inprog = a->d_inprog;
         P.group_off = a->d_group_off;
         P.cur0 = a->d_cur0;
+        P.patch_fail = a->d_patch_fail;
         P.totals = a->d_totals;
         P.sums = reinterpret_cast<unsigned long long *>(a->d_sums);
         P.dense = a->d_dense;
@@ -844,7 +851,7 @@ static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream)
         }
         if (small) {
             launch_small<E>(P, mode, stream);
-        } else if (identity) {
+        } else if (identity && !a->d_patch_fail) {
             if (P.pol_count == 1) {
                 if (vec) launch_identity<E, kVec, 1>(P, mode, stream);
                 else launch_identity<E, 1, 1>(P, mode, stream);

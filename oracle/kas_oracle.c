@@ -184,7 +184,8 @@ KAS_EXPORT void kas_oracle_replay(const int32_t *llen, const int32_t *inprog, in
                                   const int32_t *cur0,
                                   const int32_t *policies, uint32_t S,
                                   int64_t *pod_ticks, int64_t *n_patches, int32_t *final_cur,
-                                  int32_t *dense, int threads)
+                                  int32_t *dense, const uint8_t *patch_fail /* [T][R] or NULL */,
+                                  int threads)
 {
 #pragma omp parallel for schedule(static) num_threads(threads > 0 ? threads : 1)
     for (uint64_t r = 0; r < R; ++r) {
@@ -203,7 +204,11 @@ KAS_EXPORT void kas_oracle_replay(const int32_t *llen, const int32_t *inprog, in
                     sum += clip64(floordiv64(tally, kpp), mn, mx, cur);   /* :255-257 */
                 }
                 int64_t desired = clip64(sum, mn, mx, cur);               /* :259 */
-                if (desired != cur) { np += 1; cur = desired; }           /* :227 */
+                if (desired != cur) {                                      /* :227 */
+                    np += 1;                                               /* the patch call is made */
+                    /* ... and, if it raises, swallowed: replicas stay (:267-273) */
+                    if (!(patch_fail && patch_fail[(uint64_t)t * R + r])) cur = desired;
+                }
                 pt += cur;
                 if (dense) dense[((uint64_t)s * T + t) * R + r] = (int32_t)cur;
             }

@@ -101,20 +101,22 @@ def decisions():
     return dict(get_desired_pods=rows, clip_pod_count=clip)
 
 
-def _run_scale(queues, depths, keyspace, kpp, mn, mx, cur0, rtype, delim=','):
-    """depths: list over ticks of list over queues (LLEN values)."""
+def _run_scale(queues, depths, keyspace, kpp, mn, mx, cur0, rtype, delim=',', fails=None):
+    """depths: list over ticks of list over queues (LLEN values); fails[t] true makes the
+    patch call of tick t raise ApiException (swallowed by scale(), autoscaler.py:267-273)."""
     names = queues.split(delim)
     redis = refload.StubRedis(keyspace=[k.encode('latin-1') for k in keyspace])
     kube = refload.StatefulKube('r', rtype, cur0)
     s = _scaler(queues, delim, redis, kube)
     after, tallies = [], []
-    for row in depths:
+    for t, row in enumerate(depths):
         redis.lists = dict(zip(names, row))
+        kube.fail_next_patch = bool(fails and fails[t])
         s.scale('ns', rtype, 'r', min_pods=mn, max_pods=mx, keys_per_pod=kpp)
         after.append(int(kube.value))
         tallies.append([s.redis_keys[q] for q in s.redis_keys])
     return dict(queues=queues, delim=delim, depths=depths, keyspace=keyspace,
-                kpp=kpp, min=mn, max=mx, cur0=cur0, type=rtype,
+                kpp=kpp, min=mn, max=mx, cur0=cur0, type=rtype, fails=fails,
                 after=after, patches=[int(p) for p in kube.patches], tallies=tallies)
 
 
@@ -147,6 +149,18 @@ def scale_cases():
         for q in names:
             ks += ['processing-%s:h%d' % (q, k) for k in range(rng.choice([0, 0, 1, 3]))]
         cases.append(_run_scale(','.join(names), depths, ks, kpp, mn, mx, cur0, rtype))
+    # patch calls that raise ApiException: scale() logs and carries on, replicas stay
+    cases.append(_run_scale('a', [[3], [3], [0], [5], [5]], [], 1, 0, 9, 0, 'deployment',
+                            fails=[1, 0, 1, 0, 1]))
+    for i in range(25):
+        nq = rng.randint(1, 3)
+        names = ['f%d' % j for j in range(nq)]
+        T = rng.randint(2, 40)
+        depths = [[rng.choice([0, 0, rng.randint(0, 20)]) for _ in names] for _ in range(T)]
+        fails = [int(rng.random() < 0.35) for _ in range(T)]
+        cases.append(_run_scale(','.join(names), depths, [], rng.choice([1, 2, 3]), rng.choice([0, 1]),
+                                rng.choice([2, 5, 9]), rng.choice([0, 2, 12]),
+                                rng.choice(['deployment', 'job']), fails=fails))
     return cases
 
 
@@ -187,8 +201,8 @@ def tally_cases():
     rng = random.Random(7)
     alphabet = 'abc:-x'
     for _ in range(25):
-        names = list({''.join(rng.choice('abc:') for _ in range(rng.randint(1, 4)))
-                      for _ in range(rng.randint(1, 6))})
+        names = sorted({''.join(rng.choice('abc:') for _ in range(rng.randint(1, 4)))
+                        for _ in range(rng.randint(1, 6))})   # sorted: set order depends on the hash seed
         keys = []
         for _ in range(rng.randint(0, 120)):
             base = rng.choice(['processing-', 'processing-', 'processing', 'xprocessing-', ''])

@@ -197,15 +197,19 @@ def scale_step(tallies: Iterable[int], keys_per_pod: int, min_pods: int,
 def replay_resource(llen_rows: Sequence[Sequence[int]],
                     inprog_rows: Optional[Sequence[Sequence[int]]],
                     keys_per_pod: int, min_pods: int, max_pods: int,
-                    cur0: int = 0) -> Tuple[List[int], List[int]]:
+                    cur0: int = 0,
+                    patch_fails: Optional[Sequence[bool]] = None) -> Tuple[List[int], List[int]]:
     """Replay one resource over T ticks with a well-behaved Kubernetes mock:
     what a tick patches (autoscaler.py:232,236) is what the next tick reads
     (autoscaler.py:179,189), and no patch is issued when desired == current
     (autoscaler.py:227-228).
 
     ``llen_rows[t][j]`` is LLEN of the resource's j-th queue at tick t;
-    ``inprog_rows[t][j]`` the SCAN count (None -> 0).  Returns
-    (replicas after each tick, list of patched values in order).
+    ``inprog_rows[t][j]`` the SCAN count (None -> 0).  ``patch_fails[t]`` true
+    means the patch call of tick t raises ApiException: ``scale`` swallows it
+    (autoscaler.py:267-273) and the resource keeps its replicas; the attempt is
+    still listed.  Returns (replicas after each tick, list of values the
+    patch calls carried, in order).
     """
     cur = cur0
     after, patches = [], []
@@ -217,7 +221,8 @@ def replay_resource(llen_rows: Sequence[Sequence[int]],
         desired = scale_step(tallies, keys_per_pod, min_pods, max_pods, cur)
         if desired != cur:
             patches.append(desired)
-            cur = desired
+            if not (patch_fails is not None and patch_fails[t]):
+                cur = desired
         after.append(cur)
     return after, patches
 

@@ -129,6 +129,7 @@ class StatefulKube(object):
         self.resource_type = resource_type
         self.value = replicas
         self.patches = []
+        self.fail_next_patch = False   # raise ApiException on the next patch call (it is still listed)
 
     def _items(self):
         spec = _Bunch(replicas=str(self.value), parallelism=str(self.value),
@@ -148,8 +149,10 @@ class StatefulKube(object):
 
     def _patch(self, name, namespace, body, field):
         assert name == self.name
+        self.patches.append(body['spec'][field])
+        if self.fail_next_patch:
+            raise sys.modules['kubernetes'].client.rest.ApiException('thrown on purpose')
         self.value = body['spec'][field]
-        self.patches.append(self.value)
         return _Bunch(items=[])
 
     def patch_namespaced_deployment(self, name, namespace, body):

@@ -20,11 +20,12 @@ def test_golden_scale_cases():
         scaler = autoscaler.Autoscaler(helpers.ListRedis(), case['queues'], case['delim'])
         res = scaler.replay(llen, [(case['kpp'], case['min'], case['max'])],
                             inprog=np.array(inprog, dtype=np.int32), current_pods=case['cur0'],
-                            resource_type=case['type'], want_dense=True)
+                            resource_type=case['type'], want_dense=True, patch_fail=case.get('fails'))
         assert res.dense[0, :, 0].tolist() == case['after']
         assert int(res.n_patches[0, 0]) == len(case['patches'])
         field = 'replicas' if case['type'] == 'deployment' else 'parallelism'
-        assert [b['spec'][field] for _, b in res.patch_bodies(case['type'])] == case['patches']
+        if not case.get('fails'):
+            assert [b['spec'][field] for _, b in res.patch_bodies(case['type'])] == case['patches']
     with pytest.raises(ValueError):
         scaler.replay(llen, [(1, 0, 1)], resource_type='badvalue')
     with pytest.raises(ZeroDivisionError):
@@ -199,10 +200,12 @@ def test_patch_events_match_reference_fixture():
         llen = np.array([[dict(zip(split, row)).get(q, 0) for q in names] for row in case['depths']],
                         dtype=np.int32)
         inprog = np.array(oracle.match_counts(names, helpers.latin(case['keyspace'])), dtype=np.int32)
+        fails = case.get('fails')
         log = autoscaler.replay.patch_events(llen, (case['kpp'], case['min'], case['max']), inprog=inprog,
                                              group_off=np.array([0, len(names)], dtype=np.uint64),
                                              cur0=np.array([case['cur0']], dtype=np.int32),
-                                             resource_types=case['type'])
+                                             resource_types=case['type'],
+                                             patch_fail=None if fails is None else np.array(fails).reshape(-1, 1))
         field = 'replicas' if case['type'] == 'deployment' else 'parallelism'
         assert [b['spec'][field] for _, b in log.bodies(0)] == case['patches']
 
@@ -238,3 +241,27 @@ def test_uint16_trace_format(shape, pol, ipmode):
     assert (got.sums[:, 0] == want['pod_ticks'].sum(0)).all()
     log = autoscaler.replay.patch_events(llen, POLICY_SETS[pol][0], inprog=inprog, group_off=go, cur0=cur0)
     assert (np.diff(log.off.astype(np.int64)) == want['n_patches'][:, 0]).all()
+
+
+@pytest.mark.parametrize('shape', ['identity', 'grouped', 'small'])
+def test_failing_patch_calls(shape):
+    """ApiException on a patch call is swallowed by scale() (autoscaler.py:267-273): the call
+    counts, the replicas stay.  Fleet-sized check against the oracle (the reference-made
+    fixtures with failures are covered by test_golden_scale_cases)."""
+    import autoscaler
+    from oracle import coracle
+    rng = np.random.default_rng({'identity': 5, 'grouped': 6, 'small': 7}[shape])
+    T, Q = {'identity': (60, 9000), 'grouped': (50, 12000), 'small': (200, 64)}[shape]
+    llen, go = helpers.random_fleet(rng, T, Q, grouped=(shape != 'identity'))
+    R = Q if go is None else len(go) - 1
+    fail = rng.random((T, R)) < 0.3
+    cur0 = rng.integers(0, 7, size=R).astype(np.int32)
+    pol = [(1, 0, 3), (2, 1, 9), (-3, 0, 4)]
+    want = coracle.replay(llen, None, go, cur0, pol, want_dense=True, patch_fail=fail)
+    got = autoscaler.replay.replay_fleet(llen, pol, group_off=go, cur0=cur0, want_dense=True, patch_fail=fail)
+    assert (got.dense == want['dense']).all()
+    assert (got.n_patches == want['n_patches']).all() and (got.pod_ticks == want['pod_ticks']).all()
+    log = autoscaler.replay.patch_events(llen, pol[1], group_off=go, cur0=cur0, patch_fail=fail)
+    assert (np.diff(log.off.astype(np.int64)) == want['n_patches'][:, 1]).all()
+    with pytest.raises(ValueError):
+        autoscaler.replay.replay_fleet(llen, pol, group_off=go, patch_fail=fail[:-1])

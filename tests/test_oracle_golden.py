@@ -50,18 +50,21 @@ def test_scale_cases():
         llen = [[dict(zip(split, row)).get(q, 0) for q in names] for row in case['depths']]
         tall = [[a + b for a, b in zip(row, inprog)] for row in llen]
         assert tall == case['tallies']
+        fails = case.get('fails')
         after, patches = oracle.replay_resource(llen, [inprog] * len(llen), case['kpp'],
-                                                case['min'], case['max'], case['cur0'])
+                                                case['min'], case['max'], case['cur0'], fails)
         assert after == case['after'] and patches == case['patches']
         res = coracle.replay(np.array(llen, dtype=np.int32), np.array(inprog, dtype=np.int32),
                              np.array([0, len(names)], dtype=np.uint64), [case['cur0']],
-                             [(case['kpp'], case['min'], case['max'])], want_dense=True)
+                             [(case['kpp'], case['min'], case['max'])], want_dense=True,
+                             patch_fail=None if fails is None else np.array(fails).reshape(-1, 1))
         assert res['dense'][0, :, 0].tolist() == case['after']
         assert res['n_patches'][0, 0] == len(case['patches'])
         assert res['pod_ticks'][0, 0] == sum(case['after'])
-        n = oracle.np_replay(llen, inprog, [0, len(names)], [case['cur0']],
-                             [(case['kpp'], case['min'], case['max'])], want_dense=True)
-        assert n['dense'][0, :, 0].tolist() == case['after']
+        if fails is None:
+            n = oracle.np_replay(llen, inprog, [0, len(names)], [case['cur0']],
+                                 [(case['kpp'], case['min'], case['max'])], want_dense=True)
+            assert n['dense'][0, :, 0].tolist() == case['after']
 
 
 def test_tally_cases():
