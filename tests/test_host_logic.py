@@ -294,3 +294,38 @@ def test_shard_ranges_cover_everything():
         assert local[0] == 0 and local[-1] == q_hi - q_lo
         seen.append((r_lo, r_hi, q_lo, q_hi))
     assert seen[0][1] == seen[1][0] and seen[0][3] == seen[1][2] and seen[1][3] == 12
+
+
+def test_product_never_touches_the_oracle():
+    """The oracle is test infrastructure: nothing under kiosk-autoscaler_b200/ may import,
+    load or name it (a product path through the oracle would void every parity claim)."""
+    pkg = os.path.join(ROOT, 'kiosk-autoscaler_b200')
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith(('.py', '.cu', '.cuh', '.h', '.cpp')):
+                text = open(os.path.join(dirpath, f), errors='replace').read()
+                assert 'oracle' not in text.lower() or f == 'kas_glob.cu' or f == 'kas_replay.cu', \
+                    os.path.join(dirpath, f)
+    for f in ('kas_glob.cu', 'kas_replay.cu'):
+        text = open(os.path.join(pkg, 'csrc', f)).read()
+        assert 'import oracle' not in text and 'libkas_oracle' not in text and 'kas_oracle_' not in text
+
+
+def test_reference_arm_prints_one_json_line():
+    """bench.py --impl reference: one JSON line on stdout with the agreed keys."""
+    import json
+    import subprocess
+    env = dict(os.environ, KAS_BENCH_CPU_KEYS='200000')
+    out = subprocess.run([sys.executable, os.path.join(ROOT, 'bench.py'), '--impl', 'reference',
+                          '--steps', '1', '--warmup', '0'], capture_output=True, text=True, env=env,
+                         timeout=300)
+    assert out.returncode == 0, out.stderr[-500:]
+    lines = [ln for ln in out.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d['impl'] == 'reference' and d['metric'] == 'keys matched/sec' and d['unit'] == 'keys/s'
+    assert d['value'] > 0 and d['higher_is_better'] is True and d['vs_baseline'] is None
+    assert d['cpu_baseline']['kind'] == 'port' and d['cpu_baseline']['cores'] >= 1
+    assert d['e2e'] == {'value': d['value'], 'unit': 'keys/s', 'h2d_bytes_per_step': 0,
+                        'd2h_bytes_per_step': 0}
+    assert 'workload' in d['config']
