@@ -106,37 +106,64 @@ def _is_glob(q):
     return any(ch in engine.GLOB_META for ch in engine.encode_name(q))
 
 
+MAX_PREFIX_NAME = engine.MAX_REC_BYTES - 12      # longest name a 64-byte record holds
+
+
+def _needs_glob_kernel(q):
+    """Names the prefix table cannot hold: live globs (metacharacters), names longer
+    than a record, names with a NUL byte.  The glob kernel matches them on whole keys."""
+    b = engine.encode_name(q)
+    return _is_glob(q) or len(b) > MAX_PREFIX_NAME or 0 in b
+
+
+def _glob_escape(name):
+    """A literal name as a Redis glob (only used for over-long / NUL names, which
+    by definition hold no metacharacter)."""
+    return bytes(name)
+
+
 def tally_snapshot(snapshot, queue_names, device='cuda'):
     """SCAN-count term for every queue over one snapshot: list of int, in the
     order of ``queue_names`` (autoscaler.py:69-71 of the reference).  Literal
-    names go through the prefix kernel in one pass; names holding glob
-    metacharacters -- live globs in the reference -- through the glob kernel."""
+    names go through the prefix kernel in one pass (several passes beyond 1024
+    names); names holding glob metacharacters -- live globs in the reference --
+    and names too long for a record go through the glob kernel."""
     names = list(queue_names)
     out = [0] * len(names)
-    plain = [i for i, q in enumerate(names) if not _is_glob(q)]
-    globs = [i for i, q in enumerate(names) if _is_glob(q)]
-    if plain:
-        for i, c in zip(plain, _tally_prefixes(snapshot, [names[i] for i in plain], device)):
+    plain = [i for i, q in enumerate(names) if not _needs_glob_kernel(q)]
+    globs = [i for i, q in enumerate(names) if _needs_glob_kernel(q)]
+    for lo in range(0, len(plain), engine.MAX_PREFIXES):
+        part = plain[lo:lo + engine.MAX_PREFIXES]
+        for i, c in zip(part, _tally_prefixes(snapshot, [names[i] for i in part], device)):
             out[i] = c
     if globs:
         if snapshot.off is None:
-            raise ValueError('queue names with glob metacharacters need the whole keys; this '
-                             'snapshot only holds fixed-width heads')
+            raise ValueError('queue names with glob metacharacters (or longer than %d bytes) need '
+                             'the whole keys; this snapshot only holds fixed-width heads'
+                             % MAX_PREFIX_NAME)
         d_blob, d_off = snapshot.device_blob(device)
-        pats = [b'processing-' + bytes(engine.encode_name(names[i])) + b':*' for i in globs]
-        counts = engine.glob_count(d_blob, d_off, len(snapshot), pats, sep_bytes=snapshot.sep_bytes)
-        for i, c in zip(globs, engine.counts_to_host(counts)):
-            out[i] = int(c)
+        for lo in range(0, len(globs), 256):
+            part = globs[lo:lo + 256]
+            pats = [b'processing-' + _glob_escape(engine.encode_name(names[i])) + b':*' for i in part]
+            counts = engine.glob_count(d_blob, d_off, len(snapshot), pats, sep_bytes=snapshot.sep_bytes)
+            for i, c in zip(part, engine.counts_to_host(counts)):
+                out[i] = int(c)
     return out
 
 
 def _tally_prefixes(snapshot, names, device):
     torch = engine.require_cuda()
     rec_bytes = engine.rec_bytes_for(names)
-    if rec_bytes > engine.MAX_REC_BYTES:
-        raise engine.KasError(engine.KAS_ERR_UNSUPPORTED, 'tally',
-                              'queue names longer than %d bytes' % (engine.MAX_REC_BYTES - 12))
-    table = torch.from_numpy(engine.build_prefix_table(names, rec_bytes)).to(device)
+    try:
+        image = engine.build_prefix_table(names, rec_bytes)
+    except engine.KasError as err:
+        # the table of this many names does not fit shared memory at this record width
+        if err.status != engine.KAS_ERR_UNSUPPORTED or len(names) < 2:
+            raise
+        half = len(names) // 2
+        return (_tally_prefixes(snapshot, names[:half], device) +
+                _tally_prefixes(snapshot, names[half:], device))
+    table = torch.from_numpy(image).to(device)
     heads = snapshot.device_heads(rec_bytes, device)
     counts = engine.match_count(heads, len(snapshot), rec_bytes, table, len(names))
     return [int(c) for c in engine.counts_to_host(counts)]

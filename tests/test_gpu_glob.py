@@ -80,3 +80,20 @@ def test_glob_equals_prefix_kernel_on_literal_names():
                                 ['pre*', 'predict'])
     with pytest.raises(ValueError):
         snapshot.tally_snapshot(snapshot.KeySnapshot.from_heads(snap.heads(32)), ['pre*'])
+
+
+def test_names_beyond_the_prefix_table_limits():
+    """Names longer than a 64-byte record, a NUL inside a name, and more than 1024 names
+    (also at a width where 1024 do not fit shared memory) still tally like the reference."""
+    from autoscaler import snapshot
+    from oracle import oracle
+    long_name = 'q' * 70
+    names = ['predict', long_name, 'a\x00b', 'track'] + ['n%04d' % i for i in range(1500)] + ['w' * 50]
+    keys = [b'processing-predict:1', b'processing-' + long_name.encode() + b':x',
+            b'processing-' + long_name.encode()[:-1] + b':x', b'processing-a\x00b:z', b'processing-a:z',
+            b'processing-n0007:1', b'processing-n1499:', b'processing-n1499', b'processing-' + b'w' * 50 + b':k']
+    keys = keys * 3
+    snap = snapshot.KeySnapshot.from_keys(keys)
+    got = snapshot.tally_snapshot(snap, names)
+    assert got == oracle.match_counts(names, keys)
+    assert sum(got) == 3 * 6
