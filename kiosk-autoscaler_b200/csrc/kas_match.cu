@@ -132,9 +132,9 @@ struct Matcher {
     }
 
     // Is region[0..L] an entry?  One look at its home slot (two for a two-slot
-    // table), no probing (kas_table.h).  Returns the entry's meta word, or
-    // kNoQueue when it is not an entry.
-    __device__ __forceinline__ uint32_t lookup(const uint32_t (&r)[RW], int L) const {
+    // table), no probing (kas_table.h).  On a hit: the entry's queue id (kNoQueue for
+    // a virtual entry) and whether a longer entry continues it.
+    __device__ __forceinline__ bool lookup(const uint32_t (&r)[RW], int L, uint32_t &qid, bool &ext) const {
         uint32_t m[RWP];
         const uint4 *mrow = reinterpret_cast<const uint4 *>(sm.masks + (uint32_t)L * RWP);
 #pragma unroll
@@ -164,7 +164,9 @@ struct Matcher {
         };
         bool hit = fetch(hash_slot_a(tag, slot_shift));
         if (two_slot && !hit) hit = fetch(hash_slot_b(tag, slot_shift));
-        return hit ? w[RW + 1] : kNoQueue;
+        ext = w[RW] != 0u;
+        qid = w[RW + 1];
+        return hit;
     }
 
     // Nested queue names ("predict" and "predict:zstack") make a key's walk go on
@@ -221,11 +223,11 @@ struct Matcher {
         if (mine && rest != 0) {
             L = first_bit<mask_t>(rest);
             rest &= rest - 1;
-            const uint32_t meta = lookup(r, L);
-            if (meta != kNoQueue) {
-                const uint32_t q = meta & ~kExtFlag;
-                if (q != kVirtualQueue) atomicAdd(&sm.hist[q], 1u);
-                more = (meta & kExtFlag) && rest != 0;
+            uint32_t q;
+            bool ext;
+            if (lookup(r, L, q, ext)) {
+                if (q != kNoQueue) atomicAdd(&sm.hist[q], 1u);
+                more = ext && rest != 0;
             }
         }
         park(more, r, L);
@@ -243,12 +245,11 @@ struct Matcher {
         if (literal && colons != 0) {
             L = first_bit<mask_t>(colons);
             colons &= colons - 1;
-            const uint32_t meta = lookup(r, L);
-            if (meta != kNoQueue) {
-                const uint32_t id = meta & ~kExtFlag;
-                if (id != kVirtualQueue) q = id;
-                more = (meta & kExtFlag) && colons != 0;   // may over-report: resume() re-checks exactly
-            }
+            uint32_t id;
+            bool ext;
+            const bool hit = lookup(r, L, id, ext);
+            q = hit ? id : kNoQueue;                      // a virtual entry carries kNoQueue itself
+            more = hit && ext && colons != 0;             // may over-report: resume() re-checks exactly
         }
         park(more, r, L);
         while (waiting >= 32u) resume();
@@ -509,7 +510,7 @@ int kas_prefix_table_build(const uint8_t *names, const uint32_t *name_off, uint3
         for (uint32_t k = 0; k < RW; ++k) masks[(size_t)L * RWP + k] = word_mask((int)k, (int)L + 1);
 
     // masked words, unfinished hash and meta of every entry
-    struct Packed { uint32_t m[(KAS_MAX_REC_BYTES + 3) / 4]; uint32_t h, nbytes, meta; };
+    struct Packed { uint32_t m[(KAS_MAX_REC_BYTES + 3) / 4]; uint32_t h, nbytes, q; bool ext; };
     std::vector<Packed> packed;
     uint64_t len_mask = 0;
     for (const auto &kv : entries) {
@@ -524,7 +525,8 @@ int kas_prefix_table_build(const uint8_t *names, const uint32_t *name_off, uint3
                       ((uint32_t)buf[4 * k + 2] << 16) | ((uint32_t)buf[4 * k + 3] << 24);
             pk.h += pk.m[k] * hash_word_constant((int)k);
         }
-        pk.meta = kv.second.q | (kv.second.ext ? kExtFlag : 0u);
+        pk.q = kv.second.q == kVirtualQueue ? kNoQueue : kv.second.q;
+        pk.ext = kv.second.ext;
         len_mask |= 1ull << (pk.nbytes - 1);
         packed.push_back(pk);
     }
@@ -578,8 +580,8 @@ int kas_prefix_table_build(const uint8_t *names, const uint32_t *name_off, uint3
         const Packed &pk = packed[owner[sl]];
         uint32_t *e = slots + (size_t)sl * EW;
         for (uint32_t k = 0; k < RW; ++k) e[k] = pk.m[k];
-        e[RW] = 0u;
-        e[RW + 1] = pk.meta;
+        e[RW] = pk.ext ? 1u : 0u;
+        e[RW + 1] = pk.q;
     }
     t[0] = kTableMagic;
     t[1] = rec_bytes;

@@ -29,8 +29,8 @@
 //   length masks: (rec_bytes-8) rows of RWP words; row P holds, for each region
 //       word, the mask of the bytes below P+1 (RWP = region words rounded up to 4)
 //   entries: n_slots rows of EW words: RW region words (masked, zero padded),
-//       one reserved word, meta (queue id | ext << 31, queue id 0x7FFFFFFE =
-//       virtual).  EW = RW + 2 is a multiple of 4, so a row is read with 128-bit
+//       a word that is non-zero when a longer entry continues this one (ext), and
+//       the queue id (0xFFFFFFFF for a virtual entry).  EW = RW + 2 is a multiple of 4, so a row is read with 128-bit
 //       shared loads.
 #pragma once
 #include <stdint.h>
@@ -43,7 +43,7 @@
 
 namespace kas {
 
-constexpr uint32_t kTableMagic = 0x4B415334u;  // "KAS4"
+constexpr uint32_t kTableMagic = 0x4B415335u;  // "KAS5"
 constexpr uint32_t kTableHeaderWords = 8;
 constexpr uint32_t kLiteralLen = 11;           // strlen("processing-")
 // The compared "region" of a record starts at byte 8, i.e. at the last three bytes
@@ -51,8 +51,7 @@ constexpr uint32_t kLiteralLen = 11;           // strlen("processing-")
 // byte shuffling on the device), and "ng-" is simply part of every stored string.
 constexpr uint32_t kRegionStart = 8;
 constexpr uint32_t kRegionLiteral = kLiteralLen - kRegionStart;   // 3
-constexpr uint32_t kVirtualQueue = 0x7FFFFFFEu;   // with the ext flag still != kNoQueue (the "not an entry" answer)
-constexpr uint32_t kExtFlag = 0x80000000u;
+constexpr uint32_t kVirtualQueue = 0x7FFFFFFEu;   // builder-side marker of an entry without a queue
 
 KAS_HD constexpr uint32_t region_words(uint32_t rec_bytes) { return (rec_bytes - kRegionStart) / 4; }
 KAS_HD constexpr uint32_t region_words_padded(uint32_t rec_bytes) { return (region_words(rec_bytes) + 3) / 4 * 4; }
