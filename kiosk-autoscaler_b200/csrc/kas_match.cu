@@ -29,9 +29,11 @@ namespace kas {
 #define KAS_MATCH_U 2      // keys per thread per step (32-byte records); two steps are in flight
 #endif
 #ifndef KAS_MATCH_MINB
-#define KAS_MATCH_MINB 4   // resident blocks per SM the register budget is held to
+#define KAS_MATCH_MINB 1   // resident blocks per SM the register budget is held to (narrow records)
 #endif
-constexpr int kMatchThreads = 256;
+#ifndef KAS_MATCH_THREADS
+#define KAS_MATCH_THREADS 1024   // one big block per SM: the table is staged once per SM (narrow records)
+#endif
 constexpr uint32_t kNoQueue = 0xFFFFFFFFu;
 constexpr size_t kMaxMatchSmem = 200 * 1024;
 
@@ -64,6 +66,7 @@ struct MatchCfg {
     static constexpr int kEW = kRW + 2;                                    // entry words
     static constexpr int kRows = 16 * NCHUNK - (int)kRegionStart;           // colon positions inside the region
     static constexpr int kKeysPerThread = NCHUNK <= 2 ? KAS_MATCH_U : 1;
+    static constexpr int kThreads = NCHUNK <= 2 ? KAS_MATCH_THREADS : 256;
     static constexpr int kMinBlocks = NCHUNK <= 2 ? KAS_MATCH_MINB : 3;    // wide records need the registers
     using mask_t = typename std::conditional<(kRows <= 32), uint32_t, uint64_t>::type;   // one bit per colon position
     // a deferred walk: region words + the position already dealt with, padded to 128-bit rows
@@ -258,7 +261,7 @@ struct Matcher {
 };
 
 template <int NCHUNK, bool WIDE>
-__global__ void __launch_bounds__(kMatchThreads, MatchCfg<NCHUNK>::kMinBlocks)
+__global__ void __launch_bounds__(MatchCfg<NCHUNK>::kThreads, MatchCfg<NCHUNK>::kMinBlocks)
 match_count_kernel(const uint8_t *__restrict__ heads, uint64_t n_keys,
                    const uint32_t *__restrict__ tbl, uint32_t n_prefix, uint32_t n_slots,
                    uint32_t log2_slots, uint32_t one, unsigned long long *__restrict__ counts) {
@@ -385,7 +388,8 @@ static uint32_t item_words(uint32_t rec_bytes) {
 }
 
 static size_t match_smem_bytes(uint32_t n_prefix, uint32_t rec_bytes) {
-    const size_t queues = (size_t)(kMatchThreads / 32) * kQueueItems * item_words(rec_bytes);
+    const size_t threads = rec_bytes <= 32 ? KAS_MATCH_THREADS : 256;   // MatchCfg<>::kThreads
+    const size_t queues = (threads / 32) * kQueueItems * item_words(rec_bytes);
     return (image_words(n_prefix, rec_bytes) + ((n_prefix + 3u) & ~3u) + queues) * sizeof(uint32_t);
 }
 
@@ -402,16 +406,16 @@ static int launch_match(const void *d_heads, uint64_t n_keys, const void *d_tbl,
     if (smem > 48 * 1024)
         KAS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
-    KAS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kMatchThreads, smem));
+    KAS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, MatchCfg<NCHUNK>::kThreads, smem));
     if (per_sm < 1) return KAS_ERR_UNSUPPORTED;
     const int sms = sm_count();
     if (sms <= 0) return KAS_ERR_CUDA;
-    const uint64_t tile = (uint64_t)kMatchThreads * MatchCfg<NCHUNK>::kKeysPerThread;
+    const uint64_t tile = (uint64_t)MatchCfg<NCHUNK>::kThreads * MatchCfg<NCHUNK>::kKeysPerThread;
     uint64_t want = (n_keys + tile - 1) / tile;
     uint64_t grid = (uint64_t)sms * per_sm;
     if (want < grid) grid = want;
     if (grid == 0) grid = 1;
-    kern<<<(unsigned)grid, kMatchThreads, smem, stream>>>(
+    kern<<<(unsigned)grid, MatchCfg<NCHUNK>::kThreads, smem, stream>>>(
         static_cast<const uint8_t *>(d_heads), n_keys, static_cast<const uint32_t *>(d_tbl),
         n_prefix, n_slots, log2_slots, 1u, reinterpret_cast<unsigned long long *>(d_counts));
     KAS_CUDA_TRY(cudaGetLastError());
