@@ -210,6 +210,17 @@ def run_ours(args):
         raise SystemExit('bench.py needs a CUDA device (there is no CPU fallback); '
                          'use --impl reference for the CPU arm')
     torch.cuda.set_device(local)
+    numa = 'unchanged'
+    if world > 1:
+        # keep this rank's host threads (and the pinned memory they first touch) on the CPUs next
+        # to its GPU: the end-to-end leg is bound by the host-to-device copy
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local))
+            numa = 'cpu affinity of the GPU (NVML)'
+        except Exception as err:   # not fatal: only the e2e leg is affected
+            numa = 'unchanged (%s)' % type(err).__name__
     if world > 1:
         dist.init_process_group('nccl', device_id=torch.device('cuda', local))
     dev = torch.device('cuda', local)
@@ -440,7 +451,7 @@ def run_ours(args):
             'cpu_baseline': cpu, 'e2e': e2e, 'gpu_launches': args.steps, 'clocks': clocks,
             'replay': rep, 'ingest': ingest,
             'checks': {'keys_matched_fraction': float(counts_box.sum()) / (world * n),
-                       'host_generation_s': gen_s,
+                       'host_generation_s': gen_s, 'host_affinity': numa,
                        'local_counts_sum': int(local_counts.sum())},
         }
         emit(line)
