@@ -5,8 +5,8 @@
 // Python-side count PER QUEUE) with ONE streaming pass over the snapshot for
 // all queues.  HBM-bound integer/byte work: each key's rec_bytes are read
 // exactly once with 128/256-bit loads, the queue table lives in shared memory,
-// counts are aggregated warp -> block (shared) -> grid (one 64-bit atomic per
-// queue per block).
+// counts are aggregated lane -> block (shared-memory atomics) -> grid (one 64-bit
+// atomic per queue per block).
 //
 // Per key: test the 11-byte literal, find the ':' bytes of the name region
 // with byte-parallel arithmetic, and look the text up to the first ':' up in
@@ -332,20 +332,16 @@ match_count_kernel(const uint8_t *__restrict__ heads, uint64_t n_keys,
             }
         }
     };
-    // The warp histogram of record u is issued (MATCH.ANY) as soon as its queue id is
-    // known and consumed one record later, so its latency hides behind the next lookup.
-    uint32_t pend_q = kNoQueue, pend_peers = 0u;
-    auto settle = [&]() {
-        if (pend_q != kNoQueue && (pend_peers & mt.lanemask_lt) == 0u)   // lowest lane of each group adds
-            atomicAdd(&mt.sm.hist[pend_q], (uint32_t)__popc(pend_peers));
-    };
+    // Block histogram: one shared-memory atomic per counting lane.  Measured against a
+    // warp-aggregated form (MATCH.ANY + popc, one atomic per distinct queue per warp) this
+    // is 6 % faster at 64 queues and no slower at one or two queues: the atomic unit
+    // already serialises lanes that hit the same word, and the ten instructions of the
+    // aggregation cost more integer-pipe time than they save.
     auto examine = [&](const uint32_t (&x)[U][XW]) {
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             const uint32_t q = mt.first_step(x[u]);
-            settle();
-            pend_q = q;
-            pend_peers = __match_any_sync(0xFFFFFFFFu, q);
+            if (q != kNoQueue) atomicAdd(&mt.sm.hist[q], 1u);
         }
     };
     const uint64_t tile = (uint64_t)blockDim.x * U;
@@ -362,7 +358,6 @@ match_count_kernel(const uint8_t *__restrict__ heads, uint64_t n_keys,
         examine(xb);
         base += stride;
     }
-    settle();
     while (mt.waiting) mt.resume();
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < n_prefix; i += blockDim.x) {

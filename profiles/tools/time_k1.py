@@ -11,7 +11,7 @@ import bench  # noqa: E402
 from autoscaler import engine  # noqa: E402
 
 n = int(os.environ.get('KAS_BENCH_KEYS', 100_000_000))
-names = bench.queue_names() if os.environ.get('KAS_NAMES', 'c2') == 'c2' else ['predict', 'track']
+names = {'c2': bench.queue_names(), 'two': ['predict', 'track'], 'one': ['predict']}[os.environ.get('KAS_NAMES', 'c2')]
 W = engine.rec_bytes_for(names)
 host = torch.empty(n * W, dtype=torch.uint8).pin_memory()
 engine.synth_keys_host(2, 0, n, names, rec_bytes=W, heads_out=host)
