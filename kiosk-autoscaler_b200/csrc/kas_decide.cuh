@@ -83,6 +83,33 @@ __device__ __forceinline__ int32_t finish_simple(uint32_t q, const PolDev &p, in
     const int32_t d = max((int32_t)min(q, (uint32_t)p.mx), p.mn);
     return d > 0 ? max(d, cur) : d;
 }
+// finish_simple without the compare-and-select, for the policy sweep (integer ALU bound).
+// d0 = max(min(q, max), min) is 0 exactly when min <= 0 and (q == 0 or max == 0); in that
+// case the answer is 0, in every other case max(d0, cur).  With
+//   keep = min(q + (min > 0), max > 0)            (0 or 1; shared by policies that agree on
+//                                                  keys_per_pod, min > 0 and max > 0)
+// both cases are max(min(q, max), min, cur * keep): one multiply on the FMA pipe and one
+// three-input maximum (VIMNMX3) on the ALU pipe.
+struct KeepTerm {
+    uint32_t add;   // 1 when min_pods > 0
+    uint32_t lim;   // 1 when max_pods > 0
+};
+__device__ __forceinline__ KeepTerm keep_term(const PolDev &p) {
+    KeepTerm k;
+    k.add = p.mn > 0 ? 1u : 0u;
+    k.lim = p.mx > 0 ? 1u : 0u;
+    return k;
+}
+__device__ __forceinline__ uint32_t keep_factor(uint32_t q, const KeepTerm &k, uint32_t one) {
+    return min(q * one + k.add, k.lim);   // q <= 2^32 - 2, so q + 1 does not wrap
+}
+__device__ __forceinline__ int32_t finish_simple3(uint32_t q, uint32_t keep, const PolDev &p, int32_t cur) {
+#ifdef KAS_NO_MAX3
+    return max(max((int32_t)min(q, (uint32_t)p.mx), p.mn), cur * (int32_t)keep);
+#else
+    return __vimax3_s32((int32_t)min(q, (uint32_t)p.mx), p.mn, cur * (int32_t)keep);
+#endif
+}
 template <bool K1>
 __device__ __forceinline__ int32_t decide_simple(uint32_t tally, const PolDev &p, int32_t cur) {
     return finish_simple(quotient_simple<K1>(tally, p), p, cur);

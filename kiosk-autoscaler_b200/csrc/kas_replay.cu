@@ -338,6 +338,7 @@ constexpr int kSweepCols = 128;                 // resources per block (32 lanes
 constexpr int kSweepTileRows = 64;              // ticks per tile when a block covers one group of columns
 constexpr int kSweepStages = 3;                 // tiles in shared memory (one block barrier per tile)
 constexpr int kSweepSP = 2;                     // policies per warp
+constexpr int32_t kSweepNarrowBound = 1 << 24;  // x (at most 64 ticks per tile) stays below 2^32
 constexpr int kSweepMaxWarps = kMaxPoliciesPerLaunch / kSweepSP;   // 16
 
 __device__ __forceinline__ void cp_async_16(void *smem_dst, const void *gmem_src) {
@@ -372,7 +373,7 @@ __device__ __forceinline__ void bulk_copy_g2s(void *smem_dst, const void *gmem_s
                    "r"((uint32_t)__cvta_generic_to_shared(bar)) : "memory");
 }
 
-template <typename E, bool TICKIP, int MODE>
+template <typename E, bool TICKIP, int MODE, bool NARROW>
 __global__ void __launch_bounds__(32 * kSweepMaxWarps, 1)
 replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
     constexpr int SP = kSweepSP, VEC = 4;
@@ -401,12 +402,15 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
     bool live[SP];
 #pragma unroll
     for (int s = 0; s < SP; ++s) {
-        live[s] = pbase + s < P.pol_count;
-        pol[s] = P.pol[live[s] ? pbase + s : P.pol_count - 1];
+        live[s] = pbase + s < P.pol_count && P.pol_index[pbase + s] != 0xFFFFu;   // not an empty slot
+        pol[s] = P.pol[pbase + s < P.pol_count ? pbase + s : P.pol_count - 1];
     }
     const bool dense = P.dense != nullptr;
     const int32_t one = P.one;
-    const bool same_kpp = pol[0].magic == pol[SP - 1].magic && pol[0].k1 == pol[SP - 1].k1;
+    // The host pairs policies that agree on keys_per_pod, min > 0 and max > 0 (an odd group
+    // is closed by an empty slot), so a warp's two policies share the quotient and the keep
+    // factor: both come from pol[0].
+    const KeepTerm keep = keep_term(pol[0]);
     int32_t cur[SP][VEC];
     long long pt[SP][VEC];
     uint32_t np[SP][VEC];
@@ -418,12 +422,27 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
 #pragma unroll
         for (int s = 0; s < SP; ++s) { cur[s][v] = c0; pt[s][v] = 0; np[s][v] = 0u; }
     }
+    int32_t ipq_sign = 0;     // negative when a per-queue in-progress count is
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) ipq_sign |= ipq[v];
+    // NARROW: pod-ticks of the ticks of one tile are summed in 32 bits and added to the
+    // 64-bit totals once per tile.  The host picks it when that cannot wrap: under the
+    // simple arithmetic a decision is at most max(max_pods, the pods at the start), so
+    // max_pods < kSweepNarrowBound for every policy and no cur0 suffices.  (One kernel per
+    // choice: with both forms in one kernel the compiler merges them into the slower.)
+    uint32_t pa[SP][VEC];
+#pragma unroll
+    for (int s = 0; s < SP; ++s)
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) pa[s][v] = 0u;
 
     const uint32_t n_tiles = (T + tile_ticks - 1) / tile_ticks;
 #if KAS_SWEEP_TMA
     // stage tile `k` into buffer k % kSweepStages: one thread issues a bulk copy per
     // tick (the block's columns of a tick are one contiguous run) and the bytes land
-    // on the stage's mbarrier; everybody waits on that barrier's phase
+    // on the stage's mbarrier; everybody waits on that barrier's phase.  (A variant
+    // without the block barrier -- warps count themselves out of a tile and the last
+    // one refills it -- measured 2 % slower.)
     __shared__ uint64_t bars[kSweepStages];
     if (threadIdx.x == 0) {
 #pragma unroll
@@ -503,29 +522,32 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
             auto ticks = [&](uint32_t t, auto gtag) {
                 constexpr int G = decltype(gtag)::value;
                 int32_t l[G][VEC], ip[G][VEC];
-                int32_t any = 0;
+                int32_t any = ipq_sign;
 #pragma unroll
                 for (int g = 0; g < G; ++g) {
                     read4(tl + (t + g) * row_elems, l[g]);
                     if (TICKIP) {
                         read4(ti + (t + g) * row_elems, ip[g]);
+#pragma unroll
+                        for (int v = 0; v < VEC; ++v) any |= ip[g][v];
                     } else {
 #pragma unroll
                         for (int v = 0; v < VEC; ++v) ip[g][v] = ipq[v];
                     }
 #pragma unroll
-                    for (int v = 0; v < VEC; ++v) any |= l[g][v] | ip[g][v];
+                    for (int v = 0; v < VEC; ++v) any |= l[g][v];
                 }
-                auto run = [&](auto fasttag, auto sametag) {
+                auto run = [&](auto fasttag) {
                     constexpr bool FAST = decltype(fasttag)::value;
-                    constexpr bool SAMEK = decltype(sametag)::value;   // both policies divide by the same kpp
 #pragma unroll
                     for (int g = 0; g < G; ++g) {
-                        uint32_t q0[VEC];
-                        if constexpr (FAST && SAMEK) {
+                        uint32_t q0[VEC], k0[VEC];
+                        if constexpr (FAST) {
 #pragma unroll
-                            for (int v = 0; v < VEC; ++v)
+                            for (int v = 0; v < VEC; ++v) {
                                 q0[v] = quotient_simple<false>((uint32_t)l[g][v] + (uint32_t)ip[g][v], pol[0]);
+                                k0[v] = keep_factor(q0[v], keep, (uint32_t)one);
+                            }
                         }
 #pragma unroll
                         for (int s = 0; s < SP; ++s) {
@@ -533,17 +555,16 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
                             for (int v = 0; v < VEC; ++v) {
                                 const int32_t c = cur[s][v];
                                 int32_t want;
-                                if constexpr (FAST && SAMEK) {
-                                    want = finish_simple(q0[v], pol[s], c);                                           // :255-259
-                                } else if constexpr (FAST) {
-                                    want = decide_simple<false>((uint32_t)l[g][v] + (uint32_t)ip[g][v], pol[s], c);   // :255-259
+                                if constexpr (FAST) {
+                                    want = finish_simple3(q0[v], k0[v], pol[s], c);                                   // :255-259
                                 } else {
                                     want = decide_exact(l[g][v], ip[g][v], pol[s], c);                                 // :255-257
                                     want = clip32(want, pol[s].mn, pol[s].mx, c);                                     // :259
                                 }
                                 count_if_ne(np[s][v], want, c);                                                       // :227
                                 cur[s][v] = want;
-                                add_pod_ticks(pt[s][v], want, one);
+                                if constexpr (NARROW && FAST) pa[s][v] += (uint32_t)want;
+                                else add_pod_ticks(pt[s][v], want, one);
                             }
                             if (dense && live[s]) {
                                 int32_t *o = P.dense + ((uint64_t)P.pol_index[pbase + s] * T + t0 + t + g) * P.R + r0;
@@ -552,16 +573,18 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
                         }
                     }
                 };
-                if (MODE != kGeneric && any >= 0) {
-                    if (same_kpp) run(std::true_type{}, std::true_type{});
-                    else run(std::true_type{}, std::false_type{});
-                } else {
-                    run(std::false_type{}, std::false_type{});
-                }
+                if (MODE != kGeneric && any >= 0) run(std::true_type{});
+                else run(std::false_type{});
             };
             uint32_t t = 0;
             for (; t + 4 <= nt; t += 4) ticks(t, std::integral_constant<int, 4>{});
             for (; t < nt; ++t) ticks(t, std::integral_constant<int, 1>{});
+            if constexpr (NARROW) {
+#pragma unroll
+                for (int s = 0; s < SP; ++s)
+#pragma unroll
+                    for (int v = 0; v < VEC; ++v) { pt[s][v] += pa[s][v]; pa[s][v] = 0u; }
+            }
         }
     }
 #if !KAS_SWEEP_TMA
@@ -759,18 +782,25 @@ static int launch_sweep(const ReplayParams &P, int mode, cudaStream_t stream) {
     const uint64_t cols_per_block = (uint64_t)groups * kSweepCols;
     const unsigned grid = (unsigned)((P.R + cols_per_block - 1) / cols_per_block);
     const size_t smem = (size_t)(tickip ? 2 : 1) * kSweepStages * kSweepTileRows * kSweepCols * sizeof(E);
-#define KAS_LAUNCH_SWEEP(TI, MD)                                                                   \
+#define KAS_LAUNCH_SWEEP(TI, MD, NW)                                                               \
     do {                                                                                           \
-        auto kern = replay_sweep_kernel<E, TI, MD>;                                                   \
+        auto kern = replay_sweep_kernel<E, TI, MD, NW>;                                            \
         /* dynamic tiles + the static mbarriers can pass the 48 KB default */                      \
         KAS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
                                           (int)smem));                                             \
         kern<<<grid, 32 * warps, smem, stream>>>(P);                                               \
     } while (0)
+    // 32-bit pod-tick partial sums when no decision can reach kSweepNarrowBound
+    bool narrow = mode != kGeneric && P.cur0 == nullptr;
+    for (uint32_t s = 0; s < P.pol_count; ++s) narrow = narrow && P.pol[s].mx < kSweepNarrowBound;
     if (mode != kGeneric) {
-        if (tickip) KAS_LAUNCH_SWEEP(true, kSimple); else KAS_LAUNCH_SWEEP(false, kSimple);
+        if (narrow) {
+            if (tickip) KAS_LAUNCH_SWEEP(true, kSimple, true); else KAS_LAUNCH_SWEEP(false, kSimple, true);
+        } else {
+            if (tickip) KAS_LAUNCH_SWEEP(true, kSimple, false); else KAS_LAUNCH_SWEEP(false, kSimple, false);
+        }
     } else {
-        if (tickip) KAS_LAUNCH_SWEEP(true, kGeneric); else KAS_LAUNCH_SWEEP(false, kGeneric);
+        if (tickip) KAS_LAUNCH_SWEEP(true, kGeneric, false); else KAS_LAUNCH_SWEEP(false, kGeneric, false);
     }
 #undef KAS_LAUNCH_SWEEP
     return KAS_OK;
@@ -810,17 +840,31 @@ static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream)
     const bool small = a->n_resources <= kSmallMaxResources &&
                        (identity || a->n_queues <= (uint64_t)kSmallTileElems);
     // Slots of a launch in the caller's order, except under a sweep of single-queue
-    // resources: there policies are ordered by keys_per_pod, so that the two policies a
-    // warp replays usually share it (and with it the quotient).  Results are written at
-    // the caller's indices either way.
-    std::vector<uint32_t> order(a->n_policies);
-    for (uint32_t i = 0; i < a->n_policies; ++i) order[i] = i;
+    // resources: there policies are grouped by what a warp's two policies can share
+    // (keys_per_pod -> the quotient; min > 0 and max > 0 -> the keep factor), and a group
+    // of odd size is followed by an empty slot so that no pair straddles two groups.
+    // Results are written at the caller's indices either way.
+    constexpr uint32_t kEmptySlot = 0xFFFFu;           // n_policies <= 65535, so never an index
+    std::vector<uint32_t> slots(a->n_policies);
+    for (uint32_t i = 0; i < a->n_policies; ++i) slots[i] = i;
     const bool sweep_path = !small && identity && vec && a->n_policies > 1 && !a->d_patch_fail;
-    if (sweep_path)
-        std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) {
-            return a->policies[x].keys_per_pod < a->policies[y].keys_per_pod;
-        });
-    for (uint32_t first = 0; first < a->n_policies; first += kMaxPoliciesPerLaunch) {
+    if (sweep_path) {
+        auto group_less = [&](uint32_t x, uint32_t y) {
+            const kas_policy &px = a->policies[x], &py = a->policies[y];
+            if (px.keys_per_pod != py.keys_per_pod) return px.keys_per_pod < py.keys_per_pod;
+            if ((px.min_pods > 0) != (py.min_pods > 0)) return py.min_pods > 0;
+            return (px.max_pods > 0) && !(py.max_pods > 0);
+        };
+        std::vector<uint32_t> order(slots);
+        std::stable_sort(order.begin(), order.end(), group_less);
+        slots.clear();
+        for (size_t i = 0; i < order.size(); ++i) {
+            const bool new_group = i > 0 && group_less(order[i - 1], order[i]);
+            if (new_group && (slots.size() & 1u)) slots.push_back(kEmptySlot);
+            slots.push_back(order[i]);
+        }
+    }
+    for (size_t first = 0; first < slots.size(); first += kMaxPoliciesPerLaunch) {
         ReplayParams P;
         P.llen = a->d_llen;
         P.inprog = a->d_inprog;
@@ -834,17 +878,17 @@ static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream)
         P.R = a->n_resources;
         P.T = a->n_ticks;
         P.S = a->n_policies;
-        P.pol_first = first;
-        P.pol_count = a->n_policies - first < (uint32_t)kMaxPoliciesPerLaunch
-                          ? a->n_policies - first : (uint32_t)kMaxPoliciesPerLaunch;
+        P.pol_first = (uint32_t)first;
+        P.pol_count = (uint32_t)std::min<size_t>(slots.size() - first, kMaxPoliciesPerLaunch);
         P.inprog_mode = a->inprog_mode;
         P.one = 1;
         for (uint32_t s = 0; s < (uint32_t)kMaxPoliciesPerLaunch; ++s) {
             PolDev d = {0, 0, 0, 0, 0u};
-            uint32_t idx = 0;
+            uint32_t idx = kEmptySlot;
             if (s < P.pol_count) {
-                idx = order[first + s];
-                d = make_poldev(a->policies[idx]);
+                idx = slots[first + s];
+                // an empty slot repeats its partner (always the slot before it)
+                d = make_poldev(a->policies[idx != kEmptySlot ? idx : slots[first + s - 1]]);
             }
             P.pol[s] = d;
             P.pol_index[s] = (uint16_t)idx;

@@ -100,6 +100,57 @@ def test_random_fleets_vs_oracle(pol, shape, ipmode):
     assert (got.sums[:, 2] == want['final'].astype(np.int64).sum(0)).all()
 
 
+RAGGED = [(1, 0, 1), (1, 0, 0), (1, 1, 1), (2, 0, 3), (2, -1, 3), (2, 2, 5), (3, 0, 0), (3, 0, 7), (3, 1, 7),
+          (5, 0, 2 ** 24 - 1), (5, 2, 2 ** 24 - 1), (7, 0, 9), (7, 0, 9), (7, 0, 11), (9, 4, 4)]
+
+
+@pytest.mark.parametrize('width', ['narrow', 'wide_policy', 'wide_cur0', 'two_launches'])
+@pytest.mark.parametrize('dtype', ['int32', 'uint16'])
+@pytest.mark.parametrize('ipmode', [0, 2])
+def test_sweep_pairing_and_pod_tick_widths(width, dtype, ipmode):
+    """The policy-sweep kernel pairs policies by (keys_per_pod, min > 0, max > 0), closes odd
+    groups with an empty slot, and sums pod-ticks in 32 bits per tile when no decision can
+    reach 2^24: groups of odd size, max_pods == 0, duplicates, decisions right at the bound,
+    the 64-bit form (a large max_pods or given cur0), and more slots than one launch holds."""
+    import autoscaler
+    from oracle import coracle
+    rng = np.random.default_rng(hash((width, dtype, ipmode)) % (2 ** 32))
+    T, Q = 150, 8192
+    pols = list(RAGGED)
+    if width == 'wide_policy':
+        pols += [(5, 0, 2 ** 24), (11, 0, 2 ** 31 - 1), (11, 3, 2 ** 31 - 1)]
+    if width == 'two_launches':
+        pols += [(k, a, b) for k in (4, 6, 8, 10, 12, 13, 17) for a in (0, 2) for b in (0, 1, 40)][:-1]
+    hi = 2 ** 16 - 1 if dtype == 'uint16' else 2 ** 31 - 1
+    llen = rng.integers(0, 60, size=(T, Q)).astype(np.int64)
+    llen[rng.random(llen.shape) < 0.3] = 0
+    big = rng.random(Q) < 0.05                      # queues that sit at the largest count
+    llen[:, big] = hi
+    inprog = None
+    if ipmode == 2:
+        inprog = rng.integers(0, 9, size=(T, Q)).astype(np.int64)
+        inprog[:, big] = hi if dtype == 'int32' else 0
+    cur0 = None
+    if width == 'wide_cur0':
+        cur0 = rng.integers(0, 12, size=Q).astype(np.int32)
+        cur0[rng.random(Q) < 0.02] = 2 ** 31 - 1
+    np_t = np.uint16 if dtype == 'uint16' else np.int32
+    want = coracle.replay(llen.astype(np.int32), None if inprog is None else inprog.astype(np.int32),
+                          None, cur0, pols, want_dense=True)
+    got = autoscaler.replay.replay_fleet(llen.astype(np_t), pols,
+                                         inprog=None if inprog is None else inprog.astype(np_t),
+                                         cur0=cur0, want_dense=True)
+    assert (got.dense == want['dense']).all()
+    assert (got.pod_ticks == want['pod_ticks']).all()
+    assert (got.n_patches == want['n_patches']).all()
+    assert (got.final == want['final']).all()
+    assert (got.sums[:, 0] == want['pod_ticks'].sum(0)).all()
+    assert (got.sums[:, 1] == want['n_patches'].sum(0)).all()
+    if width == 'narrow':
+        # the largest decision is one below the bound, held for whole tiles
+        assert int(got.dense.max()) == 2 ** 24 - 1 or dtype == 'uint16'
+
+
 def test_synth_trace_twin():
     from autoscaler import engine
     from oracle import coracle
