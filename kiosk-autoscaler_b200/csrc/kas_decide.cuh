@@ -10,7 +10,10 @@ struct PolDev {
     int32_t mn, mx;
     int32_t neg;     // -1 when kpp < 0, else 0
     uint32_t k1;     // 1 when |kpp| == 1 (then magic == 0), else 0
+    uint32_t m32;    // ceil(2^32 / kpp) - 1 when 1 <= kpp <= kSmallKppMax, else 0 (see quotient_small)
 };
+constexpr int32_t kSmallKppMax = 1 << 14;
+constexpr uint32_t kSmallTallyTerm = 1u << 16;   // quotient_small: both terms of the tally below this
 
 // Execution modes, chosen per launch by the host from the policies alone:
 //   kGeneric  any kpp != 0, any min/max: exact 64-bit path.
@@ -26,13 +29,15 @@ enum ReplayMode { kGeneric = 0, kSimple = 1, kSimpleK1 = 2 };
 
 // Host side: the device form of one policy (keys_per_pod != 0).
 static inline PolDev make_poldev(const kas_policy &p) {
-    PolDev d = {0, 0, 0, 0, 0};
+    PolDev d = {0, 0, 0, 0, 0, 0};
     const uint64_t ak = p.keys_per_pod < 0 ? (uint64_t)(-(int64_t)p.keys_per_pod) : (uint64_t)p.keys_per_pod;
     d.magic = ak == 1 ? 0ull : (~0ull / ak) + 1ull;   // ceil(2^64/ak) (exact when ak | 2^64 too)
     d.mn = p.min_pods;
     d.mx = p.max_pods;
     d.neg = p.keys_per_pod < 0 ? -1 : 0;
     d.k1 = ak == 1 ? 1u : 0u;
+    if (p.keys_per_pod >= 1 && p.keys_per_pod <= kSmallKppMax)
+        d.m32 = (uint32_t)((0xFFFFFFFFull + ak) / ak) - 1u;   // ceil(2^32 / ak) - 1
     return d;
 }
 
@@ -76,6 +81,13 @@ __device__ __forceinline__ uint32_t quotient_simple(uint32_t tally, const PolDev
     const uint32_t lo_hi = __umulhi((uint32_t)p.magic, tally);
     const uint32_t mh = (uint32_t)(((uint64_t)(uint32_t)(p.magic >> 32) * tally + lo_hi) >> 32);
     return tally * p.k1 + mh;
+}
+// floor(tally / kpp) for tally < 2^17 and 1 <= kpp <= 2^14 as ONE multiply-high:
+// hi32((tally + 1) * m32) with m32 = ceil(2^32 / kpp) - 1 (the round-down magic number with
+// the +1 on the dividend; exact over that whole range -- checked exhaustively in
+// tests/test_host_logic.py).  The caller passes tally + 1.
+__device__ __forceinline__ uint32_t quotient_small(uint32_t tally_plus_1, const PolDev &p) {
+    return __umulhi(tally_plus_1, p.m32);
 }
 __device__ __forceinline__ int32_t finish_simple(uint32_t q, const PolDev &p, int32_t cur) {
     // if/elif clamp with 0 <= max and min <= max: the unsigned min already lands in

@@ -47,6 +47,12 @@ struct ReplayParams {
 __device__ __forceinline__ void count_if_ne(uint32_t &n, int32_t a, int32_t b) {
     asm("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %1, %2;\n\t@p add.u32 %0, %0, 1;\n\t}" : "+r"(n) : "r"(a), "r"(b));
 }
+// The same with the add issued on the FMA pipe (n = one * one + n, `one` opaque): the
+// sweep kernel is bound by the integer ALU pipe and has FMA slots to spare.
+__device__ __forceinline__ void count_if_ne_fma(uint32_t &n, int32_t a, int32_t b, int32_t one) {
+    asm("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %1, %2;\n\t@p mad.lo.u32 %0, %3, %3, %0;\n\t}"
+        : "+r"(n) : "r"(a), "r"(b), "r"(one));
+}
 
 #ifndef KAS_PT_WIDE
 #define KAS_PT_WIDE 1   // pod_ticks += want as one IMAD.WIDE (1) or as a 64-bit add (0)
@@ -349,6 +355,12 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
+#ifndef KAS_SWEEP_CNT_FMA
+#define KAS_SWEEP_CNT_FMA 0
+#endif
+#ifndef KAS_SWEEP_PA_FMA
+#define KAS_SWEEP_PA_FMA 0
+#endif
 #ifndef KAS_SWEEP_TMA
 #define KAS_SWEEP_TMA 1   // stage tiles with bulk asynchronous copies (TMA, cp.async.bulk + mbarrier); 0: cp.async
 #endif
@@ -411,6 +423,7 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
     // is closed by an empty slot), so a warp's two policies share the quotient and the keep
     // factor: both come from pol[0].
     const KeepTerm keep = keep_term(pol[0]);
+    const bool small_kpp = pol[0].m32 != 0u;
     int32_t cur[SP][VEC];
     long long pt[SP][VEC];
     uint32_t np[SP][VEC];
@@ -505,6 +518,7 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
         const E *tl = reinterpret_cast<const E *>(s_l + (k % kSweepStages) * kTileVec) + cg * kSweepCols + 4u * lane;
         const E *ti = reinterpret_cast<const E *>(s_i + (k % kSweepStages) * kTileVec) + cg * kSweepCols + 4u * lane;
         const uint32_t row_elems = row_vec * kEPP;
+        const uint32_t working = __ballot_sync(0xFFFFFFFFu, valid && (live[0] || live[SP - 1]));
         if (valid && (live[0] || live[SP - 1])) {
             // four consecutive elements out of shared memory (one 128- or 64-bit load)
             auto read4 = [](const E *p, int32_t (&o)[VEC]) {
@@ -537,15 +551,19 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
 #pragma unroll
                     for (int v = 0; v < VEC; ++v) any |= l[g][v];
                 }
-                auto run = [&](auto fasttag) {
+                auto run = [&](auto fasttag, auto smalltag) {
                     constexpr bool FAST = decltype(fasttag)::value;
+                    constexpr bool SMALLQ = decltype(smalltag)::value;   // one multiply-high per quotient
 #pragma unroll
                     for (int g = 0; g < G; ++g) {
                         uint32_t q0[VEC], k0[VEC];
                         if constexpr (FAST) {
 #pragma unroll
                             for (int v = 0; v < VEC; ++v) {
-                                q0[v] = quotient_simple<false>((uint32_t)l[g][v] + (uint32_t)ip[g][v], pol[0]);
+                                if constexpr (SMALLQ)
+                                    q0[v] = quotient_small((uint32_t)l[g][v] + (uint32_t)ip[g][v] + 1u, pol[0]);
+                                else
+                                    q0[v] = quotient_simple<false>((uint32_t)l[g][v] + (uint32_t)ip[g][v], pol[0]);
                                 k0[v] = keep_factor(q0[v], keep, (uint32_t)one);
                             }
                         }
@@ -561,9 +579,18 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
                                     want = decide_exact(l[g][v], ip[g][v], pol[s], c);                                 // :255-257
                                     want = clip32(want, pol[s].mn, pol[s].mx, c);                                     // :259
                                 }
+#if KAS_SWEEP_CNT_FMA
+                                if constexpr (FAST) count_if_ne_fma(np[s][v], want, c, one);                          // :227
+                                else count_if_ne(np[s][v], want, c);
+#else
                                 count_if_ne(np[s][v], want, c);                                                       // :227
+#endif
                                 cur[s][v] = want;
+#if KAS_SWEEP_PA_FMA
+                                if constexpr (NARROW && FAST) pa[s][v] = (uint32_t)want * (uint32_t)one + pa[s][v];
+#else
                                 if constexpr (NARROW && FAST) pa[s][v] += (uint32_t)want;
+#endif
                                 else add_pod_ticks(pt[s][v], want, one);
                             }
                             if (dense && live[s]) {
@@ -573,8 +600,12 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
                         }
                     }
                 };
-                if (MODE != kGeneric && any >= 0) run(std::true_type{});
-                else run(std::false_type{});
+                // every count of the batch below 2^16 (and keys_per_pod <= 2^14): short quotient
+                // (a whole-warp choice, so that one large count does not make the warp run both forms)
+                if (MODE != kGeneric && small_kpp && __all_sync(working, (uint32_t)any < kSmallTallyTerm))
+                    run(std::true_type{}, std::true_type{});
+                else if (MODE != kGeneric && any >= 0) run(std::true_type{}, std::false_type{});
+                else run(std::false_type{}, std::false_type{});
             };
             uint32_t t = 0;
             for (; t + 4 <= nt; t += 4) ticks(t, std::integral_constant<int, 4>{});
@@ -883,7 +914,7 @@ static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream)
         P.inprog_mode = a->inprog_mode;
         P.one = 1;
         for (uint32_t s = 0; s < (uint32_t)kMaxPoliciesPerLaunch; ++s) {
-            PolDev d = {0, 0, 0, 0, 0u};
+            PolDev d = {0, 0, 0, 0, 0u, 0u};
             uint32_t idx = kEmptySlot;
             if (s < P.pol_count) {
                 idx = slots[first + s];

@@ -329,3 +329,19 @@ def test_reference_arm_prints_one_json_line():
     assert d['e2e'] == {'value': d['value'], 'unit': 'keys/s', 'h2d_bytes_per_step': 0,
                         'd2h_bytes_per_step': 0}
     assert 'workload' in d['config']
+
+
+def test_short_quotient_magic_numbers_are_exact():
+    """The policy-sweep kernel divides small tallies with ONE multiply-high:
+    floor(t / k) == ((t + 1) * (ceil(2^32 / k) - 1)) >> 32 for every t < 2^17 and every
+    1 <= k <= 2^14 (csrc/kas_decide.cuh, quotient_small).  Checked exhaustively; the first
+    counterexamples sit right above that range (k = 2^14 fails at t = 2^18)."""
+    t = np.arange(0, 1 << 17, dtype=np.uint64)
+    for k in range(1, (1 << 14) + 1):
+        m = np.uint64(((1 << 32) + k - 1) // k - 1)
+        assert int(m) < (1 << 32)
+        q = ((t + np.uint64(1)) * m) >> np.uint64(32)
+        assert (q == t // np.uint64(k)).all(), k
+    k = 1 << 14
+    m = ((1 << 32) + k - 1) // k - 1
+    assert (((1 << 18) + 1) * m) >> 32 != (1 << 18) // k
