@@ -47,12 +47,6 @@ struct ReplayParams {
 __device__ __forceinline__ void count_if_ne(uint32_t &n, int32_t a, int32_t b) {
     asm("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %1, %2;\n\t@p add.u32 %0, %0, 1;\n\t}" : "+r"(n) : "r"(a), "r"(b));
 }
-// The same with the add issued on the FMA pipe (n = one * one + n, `one` opaque): the
-// sweep kernel is bound by the integer ALU pipe and has FMA slots to spare.
-__device__ __forceinline__ void count_if_ne_fma(uint32_t &n, int32_t a, int32_t b, int32_t one) {
-    asm("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %1, %2;\n\t@p mad.lo.u32 %0, %3, %3, %0;\n\t}"
-        : "+r"(n) : "r"(a), "r"(b), "r"(one));
-}
 
 #ifndef KAS_PT_WIDE
 #define KAS_PT_WIDE 1   // pod_ticks += want as one IMAD.WIDE (1) or as a 64-bit add (0)
@@ -355,12 +349,6 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-#ifndef KAS_SWEEP_CNT_FMA
-#define KAS_SWEEP_CNT_FMA 0
-#endif
-#ifndef KAS_SWEEP_PA_FMA
-#define KAS_SWEEP_PA_FMA 0
-#endif
 #ifndef KAS_SWEEP_TMA
 #define KAS_SWEEP_TMA 1   // stage tiles with bulk asynchronous copies (TMA, cp.async.bulk + mbarrier); 0: cp.async
 #endif
@@ -579,18 +567,10 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
                                     want = decide_exact(l[g][v], ip[g][v], pol[s], c);                                 // :255-257
                                     want = clip32(want, pol[s].mn, pol[s].mx, c);                                     // :259
                                 }
-#if KAS_SWEEP_CNT_FMA
-                                if constexpr (FAST) count_if_ne_fma(np[s][v], want, c, one);                          // :227
-                                else count_if_ne(np[s][v], want, c);
-#else
                                 count_if_ne(np[s][v], want, c);                                                       // :227
-#endif
                                 cur[s][v] = want;
-#if KAS_SWEEP_PA_FMA
-                                if constexpr (NARROW && FAST) pa[s][v] = (uint32_t)want * (uint32_t)one + pa[s][v];
-#else
+                                // (issuing these two adds on the FMA pipe instead measured 1-8 % slower)
                                 if constexpr (NARROW && FAST) pa[s][v] += (uint32_t)want;
-#endif
                                 else add_pod_ticks(pt[s][v], want, one);
                             }
                             if (dense && live[s]) {
