@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define KAS_VERSION 100 /* 0.1.0 */
+#define KAS_VERSION 101 /* 0.1.1: kas_replay_args.startup_delay */
 
 #if defined(__GNUC__)
 #define KAS_API __attribute__((visibility("default")))
@@ -220,7 +220,22 @@ typedef struct kas_replay_args {
                                    tick and resource raises ApiException, which
                                    scale() logs and swallows (autoscaler.py:267-273):
                                    the call counts in n_patches, the replicas stay   */
+    uint32_t startup_delay;     /* 0: the controller reads spec.replicas, as scale()
+                                   does (autoscaler.py:179,252).  D > 0
+                                   (<= KAS_MAX_STARTUP_DELAY): it reads
+                                   status.available_replicas, the `only_running`
+                                   branch of get_current_pods (autoscaler.py:176-177),
+                                   under a pod start-up model: a replica is available
+                                   once it has been in the spec for D ticks in a row
+                                   and gone as soon as the spec drops it,
+                                     available[t+1] = min(spec[t-D..t]), spec[<0] = cur0.
+                                   A patch is issued whenever desired != available
+                                   (:227), also when the spec already holds the value.
+                                   Outputs stay spec.replicas after the tick.  Only
+                                   deployments have this reading (a job always reports
+                                   spec.parallelism, :185-190): pass 0 for jobs.       */
 } kas_replay_args;
+#define KAS_MAX_STARTUP_DELAY 16u
 
 /* Domain: trace values and cur0 any int32; policies any int32 with
  * keys_per_pod != 0 (KAS_ERR_ZERO_DIVISION otherwise, nothing is launched).
@@ -250,7 +265,8 @@ KAS_API int kas_replay(const kas_replay_args *args, void *stream);
  * ---------------------------------------------------------------------- */
 typedef struct kas_patch_event {
     uint32_t tick;      /* tick on which the patch would have been issued   */
-    int32_t from_pods;  /* current pods read at that tick (autoscaler.py:252) */
+    int32_t from_pods;  /* current pods read at that tick (autoscaler.py:252;
+                           the available ones when startup_delay > 0)         */
     int32_t to_pods;    /* value patched                                      */
 } kas_patch_event;
 

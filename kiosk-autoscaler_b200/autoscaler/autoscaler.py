@@ -194,11 +194,13 @@ class Autoscaler(object):
 
     # ----------------------------------------------------------------- replay
     def replay(self, llen_trace, policies, inprog=None, current_pods=0,
-               resource_type='deployment', want_dense=False, patch_fail=None):
+               resource_type='deployment', want_dense=False, patch_fail=None, startup_delay=0):
         """Run ``scale`` over a whole trace for this scaler's queues (ONE
-        resource) and every policy, on the GPU.  See autoscaler.replay.replay_one."""
+        resource) and every policy, on the GPU.  See autoscaler.replay.replay_one.
+        ``startup_delay`` > 0 replays ``scale`` as if it read the pods with
+        ``only_running=True`` and a replica took that many ticks to become available."""
         from autoscaler import replay as _replay
         return _replay.replay_one(list(self.redis_keys), llen_trace, policies, inprog=inprog,
                                   current_pods=current_pods, resource_type=resource_type,
                                   managed=self.managed_resource_types, want_dense=want_dense,
-                                  patch_fail=patch_fail)
+                                  patch_fail=patch_fail, startup_delay=startup_delay)

@@ -70,7 +70,18 @@ class ReplayArgs(C.Structure):
                 ('d_group_off', C.c_void_p), ('d_cur0', C.c_void_p),
                 ('policies', C.POINTER(Policy)), ('n_policies', C.c_uint32),
                 ('d_totals', C.c_void_p), ('d_sums', C.c_void_p), ('d_dense', C.c_void_p),
-                ('trace_dtype', C.c_int32), ('d_patch_fail', C.c_void_p)]
+                ('trace_dtype', C.c_int32), ('d_patch_fail', C.c_void_p),
+                ('startup_delay', C.c_uint32)]
+
+
+MAX_STARTUP_DELAY = 16      # KAS_MAX_STARTUP_DELAY
+
+
+def _check_delay(startup_delay):
+    d = int(startup_delay)
+    if not 0 <= d <= MAX_STARTUP_DELAY:
+        raise ValueError('startup_delay must be in 0..%d ticks, got %r' % (MAX_STARTUP_DELAY, startup_delay))
+    return d
 
 
 _lib = None
@@ -357,8 +368,10 @@ def trace_dtype_of(t):
 
 def replay(d_llen, n_ticks, n_queues, policies, d_inprog=None, inprog_mode=0, d_group_off=None,
            n_resources=None, d_cur0=None, want_totals=True, want_sums=True, want_dense=False,
-           d_patch_fail=None):
+           d_patch_fail=None, startup_delay=0):
     """K2 on device tensors.  policies: sequence of (kpp, min, max).
+    ``startup_delay`` > 0: the controller reads the AVAILABLE replicas of a deployment
+    (the reference's ``only_running`` branch) under the start-up model of include/kas.h.
     The trace may be int32 or uint16 (a per-tick in-progress trace has the same type).
     Returns dict of CUDA tensors: totals (uint8 view [R][S][16]), sums int64 [S][3],
     dense int32 [S][T][R] (those requested)."""
@@ -381,7 +394,7 @@ def replay(d_llen, n_ticks, n_queues, policies, d_inprog=None, inprog_mode=0, d_
         raise TypeError('a per-tick in-progress trace must have the element type of the LLEN trace')
     args = ReplayArgs(ptr(d_llen), ptr(d_inprog), inprog_mode, n_ticks, n_queues, R,
                       ptr(d_group_off), ptr(d_cur0), parr, S, ptr(totals), ptr(sums), ptr(dense), dt,
-                      ptr(d_patch_fail))
+                      ptr(d_patch_fail), _check_delay(startup_delay))
     check(lib().kas_replay(C.byref(args), stream_ptr()), 'kas_replay')
     if want_totals:
         out['totals'] = totals
@@ -393,7 +406,7 @@ def replay(d_llen, n_ticks, n_queues, policies, d_inprog=None, inprog_mode=0, d_
 
 
 def patch_events(d_llen, n_ticks, n_queues, policy, d_inprog=None, inprog_mode=0, d_group_off=None,
-                 n_resources=None, d_cur0=None, d_patch_fail=None):
+                 n_resources=None, d_cur0=None, d_patch_fail=None, startup_delay=0):
     """Patch-event stream of one policy.  Returns (event_off numpy uint64 [R+1],
     events numpy structured [total] with tick/from_pods/to_pods)."""
     torch = require_cuda()
@@ -408,7 +421,8 @@ def patch_events(d_llen, n_ticks, n_queues, policy, d_inprog=None, inprog_mode=0
     if inprog_mode == 2 and trace_dtype_of(d_inprog) != dt:
         raise TypeError('a per-tick in-progress trace must have the element type of the LLEN trace')
     args = ReplayArgs(ptr(d_llen), ptr(d_inprog), inprog_mode, n_ticks, n_queues, R,
-                      ptr(d_group_off), ptr(d_cur0), parr, 1, None, None, None, dt, ptr(d_patch_fail))
+                      ptr(d_group_off), ptr(d_cur0), parr, 1, None, None, None, dt, ptr(d_patch_fail),
+                      _check_delay(startup_delay))
     off = torch.empty(R + 1, dtype=torch.int64, device=dev)
     nscratch = lib().kas_patch_events_scratch_bytes(R)
     scratch = torch.empty(max(nscratch, 8), dtype=torch.uint8, device=dev)

@@ -119,8 +119,16 @@ def _to_device_fail(patch_fail, torch, T, R):
     return torch.from_numpy(a).to('cuda')
 
 
+def _delay_for(resource_type, startup_delay):
+    """Only a deployment has an `only_running` reading (autoscaler.py:176-177 of the
+    reference); for a job get_current_pods returns spec.parallelism whatever the flag
+    (autoscaler.py:185-190), so the start-up delay does not apply."""
+    d = engine._check_delay(startup_delay)
+    return d if resource_type == 'deployment' else 0
+
+
 def replay_fleet(llen, policies, inprog=None, group_off=None, cur0=None, want_totals=True,
-                 want_dense=False, resource_type='deployment', patch_fail=None):
+                 want_dense=False, resource_type='deployment', patch_fail=None, startup_delay=0):
     """Replay many resources at once.
 
     llen       int32 or uint16 [T][Q] (numpy or CUDA tensor), tick-major
@@ -131,6 +139,10 @@ def replay_fleet(llen, policies, inprog=None, group_off=None, cur0=None, want_to
     patch_fail None | bool [T][R]: the patch call of that tick and resource raises
                ApiException, which ``scale`` swallows (autoscaler.py:267-273 of the
                reference): the call counts, the replicas stay
+    startup_delay  0: the controller reads spec.replicas, as ``scale`` does.  D > 0: it
+               reads status.available_replicas (``get_current_pods(only_running=True)``,
+               autoscaler.py:176-177) and a replica takes D ticks in the spec to become
+               available (model in include/kas.h); results stay spec.replicas per tick
     """
     _check_type(resource_type)
     torch = engine.require_cuda()
@@ -152,7 +164,8 @@ def replay_fleet(llen, policies, inprog=None, group_off=None, cur0=None, want_to
     d_c0 = _to_device_i32(cur0, torch, 'cur0')
     out = engine.replay(d_llen, T, Q, policies, d_inprog=d_ip, inprog_mode=mode, d_group_off=d_go,
                         n_resources=R, d_cur0=d_c0, want_totals=want_totals, want_sums=True,
-                        want_dense=want_dense, d_patch_fail=_to_device_fail(patch_fail, torch, T, R))
+                        want_dense=want_dense, d_patch_fail=_to_device_fail(patch_fail, torch, T, R),
+                        startup_delay=_delay_for(resource_type, startup_delay))
     res = ReplayResult(policies,
                        totals=engine.totals_to_host(out['totals']) if want_totals else None,
                        sums=out['sums'].cpu().numpy(),
@@ -183,13 +196,19 @@ class PatchLog(object):
 
 
 def patch_events(llen, policy, inprog=None, group_off=None, cur0=None, resource_types='deployment',
-                 patch_fail=None):
+                 patch_fail=None, startup_delay=0):
     """Patch-event stream of ONE policy over a fleet (same inputs as replay_fleet).
     ``resource_types`` is one type for all resources or a sequence with one
-    entry per resource ('deployment' / 'job'); it only selects the body field."""
+    entry per resource ('deployment' / 'job'); it only selects the body field --
+    except under ``startup_delay``, which only deployments have: a fleet replayed
+    with a delay must be of one type."""
     types = [resource_types] if isinstance(resource_types, str) else list(resource_types)
     for rt in types:
         _check_type(rt)
+    if engine._check_delay(startup_delay) and len(set(types)) > 1:
+        raise ValueError('startup_delay needs a fleet of one resource type (jobs have no '
+                         'available_replicas); replay deployments and jobs separately')
+    delay = _delay_for(types[0], startup_delay) if types else 0
     torch = engine.require_cuda()
     d_llen = _to_device_trace(llen, torch, 'llen')
     T, Q = int(d_llen.shape[0]), int(d_llen.shape[1])
@@ -210,13 +229,14 @@ def patch_events(llen, policy, inprog=None, group_off=None, cur0=None, resource_
     d_c0 = _to_device_i32(cur0, torch, 'cur0')
     off, ev = engine.patch_events(d_llen, T, Q, policy, d_inprog=d_ip, inprog_mode=mode,
                                   d_group_off=d_go, n_resources=R, d_cur0=d_c0,
-                                  d_patch_fail=_to_device_fail(patch_fail, torch, T, R))
+                                  d_patch_fail=_to_device_fail(patch_fail, torch, T, R),
+                                  startup_delay=delay)
     return PatchLog(off, ev, resource_types)
 
 
 def replay_one(queue_names, llen_trace, policies, inprog=None, current_pods=0,
                resource_type='deployment', managed=('deployment', 'job'), want_dense=False,
-               patch_fail=None):
+               patch_fail=None, startup_delay=0):
     """One resource fed by ``len(queue_names)`` queues (what one reference pod
     manages): llen_trace [T][Q] in the order of ``queue_names``."""
     _check_type(resource_type, managed)
@@ -226,7 +246,7 @@ def replay_one(queue_names, llen_trace, policies, inprog=None, current_pods=0,
     return replay_fleet(a, policies, inprog=inprog,
                         group_off=np.array([0, len(queue_names)], dtype=np.uint64),
                         cur0=np.array([current_pods], dtype=np.int64), want_dense=want_dense,
-                        resource_type=resource_type,
+                        resource_type=resource_type, startup_delay=startup_delay,
                         patch_fail=None if patch_fail is None else np.asarray(patch_fail).reshape(-1, 1))
 
 

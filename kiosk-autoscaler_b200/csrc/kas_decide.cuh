@@ -127,6 +127,23 @@ __device__ __forceinline__ int32_t decide_simple(uint32_t tally, const PolDev &p
     return finish_simple(quotient_simple<K1>(tally, p), p, cur);
 }
 
+// The `only_running` reading of a deployment (autoscaler.py:176-177) under the start-up
+// model of kas.h: the specs of the last D ticks; what is available after a tick is the
+// smallest of them and of the spec the tick leaves behind.
+struct SpecWindow {
+    int32_t h[KAS_MAX_STARTUP_DELAY];
+    __device__ __forceinline__ void init(int32_t spec0, uint32_t D) {
+        for (uint32_t i = 0; i < D; ++i) h[i] = spec0;
+    }
+    // spec after tick t -> available replicas the next tick reads
+    __device__ __forceinline__ int32_t push(int32_t spec, uint32_t t, uint32_t D) {
+        int32_t avail = spec;
+        for (uint32_t i = 0; i < D; ++i) avail = min(avail, h[i]);
+        h[t % D] = spec;
+        return avail;
+    }
+};
+
 template <int MODE>
 __device__ __forceinline__ int32_t decide(int32_t llen, int32_t inprog, const PolDev &p, int32_t cur) {
     if (MODE != kGeneric && ((llen | inprog) >= 0))

@@ -35,6 +35,7 @@ struct EventParams {
     uint64_t Q, R;
     uint32_t T;
     int32_t inprog_mode;
+    uint32_t startup_delay;          // kas_replay_args.startup_delay
     bool u16;
     PolDev pol;
 };
@@ -48,7 +49,11 @@ events_kernel(const __grid_constant__ EventParams P) {
     const PolDev pol = P.pol;
     const uint64_t q0 = P.group_off ? P.group_off[r] : r;
     const uint64_t q1 = P.group_off ? P.group_off[r + 1] : r + 1;
-    int32_t cur = P.cur0 ? P.cur0[r] : 0;
+    int32_t cur = P.cur0 ? P.cur0[r] : 0;     // what the controller reads
+    int32_t spec = cur;                       // what was last patched (differs under startup_delay)
+    const uint32_t D = P.startup_delay;
+    SpecWindow win;
+    win.init(spec, D);
     unsigned long long n = 0;
     const unsigned long long base = EMIT ? P.event_off[r] : 0ull;
     for (uint32_t t = 0; t < P.T; ++t) {
@@ -72,8 +77,9 @@ events_kernel(const __grid_constant__ EventParams P) {
                 P.events[base + n] = e;
             }
             ++n;
-            if (!(P.patch_fail && P.patch_fail[(uint64_t)t * P.R + r])) cur = want;    // :267-273
+            if (!(P.patch_fail && P.patch_fail[(uint64_t)t * P.R + r])) spec = want;   // :267-273
         }
+        cur = D ? win.push(spec, t, D) : spec;
     }
     if (!EMIT) {
         P.event_off[r + 1] = n;
@@ -200,6 +206,7 @@ static int fill_event_params(const kas_replay_args *a, uint32_t policy_index, Ev
     if (!a->d_group_off && a->n_resources != a->n_queues) return KAS_ERR_INVALID;
     if (a->n_resources > 0x7FFFFFFFull * kEventThreads) return KAS_ERR_UNSUPPORTED;
     if (a->trace_dtype != KAS_TRACE_INT32 && a->trace_dtype != KAS_TRACE_UINT16) return KAS_ERR_INVALID;
+    if (a->startup_delay > KAS_MAX_STARTUP_DELAY) return KAS_ERR_INVALID;
     const size_t elem = a->trace_dtype == KAS_TRACE_UINT16 ? 2 : 4;
     if (!aligned(a->d_llen, elem) || !aligned(a->d_inprog, a->inprog_mode == 2 ? elem : 4) ||
         !aligned(a->d_group_off, 8) || !aligned(a->d_cur0, 4))
@@ -216,6 +223,7 @@ static int fill_event_params(const kas_replay_args *a, uint32_t policy_index, Ev
     P.R = a->n_resources;
     P.T = a->n_ticks;
     P.inprog_mode = a->inprog_mode;
+    P.startup_delay = a->startup_delay;
     P.pol = make_poldev(p);
     P.u16 = a->trace_dtype == KAS_TRACE_UINT16;
     P.event_off = nullptr;

@@ -38,6 +38,7 @@ struct ReplayParams {
     uint32_t pol_first;    // global index of pol[0]
     uint32_t pol_count;    // policies in this launch
     int32_t inprog_mode;
+    uint32_t startup_delay;   // ticks a replica needs to become available (grouped kernel only)
     int32_t one;           // the constant 1, opaque to the compiler (see pod-tick accumulation)
     uint16_t pol_index[kMaxPoliciesPerLaunch];   // slot -> index of the policy in the caller's list
     PolDev pol[kMaxPoliciesPerLaunch];
@@ -247,7 +248,7 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
 }
 
 // ---- resources that own several queues (CSR groups) ------------------------
-template <typename E, int SP, int MODE>
+template <typename E, int SP, int MODE, bool DELAY>
 __global__ void __launch_bounds__(kReplayThreads)
 replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
     const uint32_t ny = (P.pol_count + SP - 1) / SP;
@@ -260,8 +261,17 @@ replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
     long long pt[SP];
     uint32_t np[SP];
     const int32_t c0 = (valid && P.cur0) ? P.cur0[r] : 0;
+    // DELAY (startup_delay > 0): cur[] is what the controller reads, the AVAILABLE replicas
+    // (autoscaler.py:176-177); spec[] is what was last patched; win[] the specs of the last
+    // D ticks.  Without it the two are the same number.
+    const uint32_t D = DELAY ? P.startup_delay : 0u;
+    int32_t spec[SP];
+    SpecWindow win[DELAY ? SP : 1];
 #pragma unroll
-    for (int s = 0; s < SP; ++s) { cur[s] = c0; pt[s] = 0; np[s] = 0u; }
+    for (int s = 0; s < SP; ++s) {
+        cur[s] = c0; spec[s] = c0; pt[s] = 0; np[s] = 0u;
+        if constexpr (DELAY) win[s].init(c0, D);
+    }
     if (valid) {
         const uint64_t q0 = P.group_off ? P.group_off[r] : r;
         const uint64_t q1 = P.group_off ? P.group_off[r + 1] : r + 1;
@@ -289,10 +299,11 @@ replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
                     const int32_t want = clip64(sum[s], p.mn, p.mx, cur[s]);          // :259
                     if (want != cur[s]) {                                             // :227
                         np[s] += 1;                                                   // the patch call is made
-                        if (!failed) cur[s] = want;                                   // raised and swallowed: :267-273
+                        if (!failed) spec[s] = want;                                  // raised and swallowed: :267-273
                     }
-                    pt[s] += cur[s];
-                    if (P.dense) P.dense[((uint64_t)P.pol_index[pbase + s] * T + t) * P.R + r] = cur[s];
+                    cur[s] = DELAY ? win[DELAY ? s : 0].push(spec[s], t, D) : spec[s];
+                    pt[s] += spec[s];
+                    if (P.dense) P.dense[((uint64_t)P.pol_index[pbase + s] * T + t) * P.R + r] = spec[s];
                 }
             }
         }
@@ -303,7 +314,7 @@ replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
                     kas_totals o;
                     o.pod_ticks = pt[s];
                     o.n_patches = np[s];
-                    o.final_current = cur[s];
+                    o.final_current = spec[s];
                     P.totals[r * P.S + P.pol_index[pbase + s]] = o;
                 }
         }
@@ -312,7 +323,7 @@ replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
 #pragma unroll
         for (int s = 0; s < SP; ++s) {
             if (pbase + s < P.pol_count) {
-                long long a = valid ? pt[s] : 0, b = valid ? (long long)np[s] : 0, c = valid ? (long long)cur[s] : 0;
+                long long a = valid ? pt[s] : 0, b = valid ? (long long)np[s] : 0, c = valid ? (long long)spec[s] : 0;
                 a = warp_sum_ll(a); b = warp_sum_ll(b); c = warp_sum_ll(c);
                 if ((threadIdx.x & 31) == 0) {
                     unsigned long long *o = P.sums + 3ull * P.pol_index[pbase + s];
@@ -530,14 +541,18 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
                     read4(tl + (t + g) * row_elems, l[g]);
                     if (TICKIP) {
                         read4(ti + (t + g) * row_elems, ip[g]);
+                        if constexpr (sizeof(E) == 4) {
 #pragma unroll
-                        for (int v = 0; v < VEC; ++v) any |= ip[g][v];
+                            for (int v = 0; v < VEC; ++v) any |= ip[g][v];
+                        }
                     } else {
 #pragma unroll
                         for (int v = 0; v < VEC; ++v) ip[g][v] = ipq[v];
                     }
+                    if constexpr (sizeof(E) == 4) {   // a uint16 element is neither negative nor >= 2^16
 #pragma unroll
-                    for (int v = 0; v < VEC; ++v) any |= l[g][v];
+                        for (int v = 0; v < VEC; ++v) any |= l[g][v];
+                    }
                 }
                 auto run = [&](auto fasttag, auto smalltag) {
                     constexpr bool FAST = decltype(fasttag)::value;
@@ -828,8 +843,13 @@ static void launch_grouped(const ReplayParams &P, int mode, cudaStream_t stream)
     const uint64_t nx = (P.R + kReplayThreads - 1) / kReplayThreads;
     const uint32_t ny = (P.pol_count + SP - 1) / SP;
     const unsigned grid = (unsigned)(nx * ny);
-    if (mode != kGeneric) replay_grouped_kernel<E, SP, kSimple><<<grid, kReplayThreads, 0, stream>>>(P);
-    else replay_grouped_kernel<E, SP, kGeneric><<<grid, kReplayThreads, 0, stream>>>(P);
+    if (P.startup_delay) {
+        if (mode != kGeneric) replay_grouped_kernel<E, SP, kSimple, true><<<grid, kReplayThreads, 0, stream>>>(P);
+        else replay_grouped_kernel<E, SP, kGeneric, true><<<grid, kReplayThreads, 0, stream>>>(P);
+    } else {
+        if (mode != kGeneric) replay_grouped_kernel<E, SP, kSimple, false><<<grid, kReplayThreads, 0, stream>>>(P);
+        else replay_grouped_kernel<E, SP, kGeneric, false><<<grid, kReplayThreads, 0, stream>>>(P);
+    }
 }
 
 }  // namespace kas
@@ -848,7 +868,8 @@ static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream)
 
     // few resources: a warp per resource with its queues staged in shared memory
     // (needs every resource's queues of one tick to fit a tile)
-    const bool small = a->n_resources <= kSmallMaxResources &&
+    const bool delayed = a->startup_delay != 0;     // the availability model lives in the grouped kernel
+    const bool small = !delayed && a->n_resources <= kSmallMaxResources &&
                        (identity || a->n_queues <= (uint64_t)kSmallTileElems);
     // Slots of a launch in the caller's order, except under a sweep of single-queue
     // resources: there policies are grouped by what a warp's two policies can share
@@ -858,7 +879,7 @@ static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream)
     constexpr uint32_t kEmptySlot = 0xFFFFu;           // n_policies <= 65535, so never an index
     std::vector<uint32_t> slots(a->n_policies);
     for (uint32_t i = 0; i < a->n_policies; ++i) slots[i] = i;
-    const bool sweep_path = !small && identity && vec && a->n_policies > 1 && !a->d_patch_fail;
+    const bool sweep_path = !small && !delayed && identity && vec && a->n_policies > 1 && !a->d_patch_fail;
     if (sweep_path) {
         auto group_less = [&](uint32_t x, uint32_t y) {
             const kas_policy &px = a->policies[x], &py = a->policies[y];
@@ -892,6 +913,7 @@ static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream)
         P.pol_first = (uint32_t)first;
         P.pol_count = (uint32_t)std::min<size_t>(slots.size() - first, kMaxPoliciesPerLaunch);
         P.inprog_mode = a->inprog_mode;
+        P.startup_delay = a->startup_delay;
         P.one = 1;
         for (uint32_t s = 0; s < (uint32_t)kMaxPoliciesPerLaunch; ++s) {
             PolDev d = {0, 0, 0, 0, 0u, 0u};
@@ -906,7 +928,7 @@ static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream)
         }
         if (small) {
             launch_small<E>(P, mode, stream);
-        } else if (identity && !a->d_patch_fail) {
+        } else if (identity && !a->d_patch_fail && !delayed) {
             if (P.pol_count == 1) {
                 if (vec) launch_identity<E, kVec, 1>(P, mode, stream);
                 else launch_identity<E, 1, 1>(P, mode, stream);
@@ -936,6 +958,7 @@ int kas_replay(const kas_replay_args *a, void *stream_v) {
     if (a->inprog_mode < 0 || a->inprog_mode > 2) return KAS_ERR_INVALID;
     if (a->inprog_mode != 0 && !a->d_inprog) return KAS_ERR_INVALID;
     if (a->trace_dtype != KAS_TRACE_INT32 && a->trace_dtype != KAS_TRACE_UINT16) return KAS_ERR_INVALID;
+    if (a->startup_delay > KAS_MAX_STARTUP_DELAY) return KAS_ERR_INVALID;
     if (!a->d_group_off && a->n_resources != a->n_queues) return KAS_ERR_INVALID;
     if (!a->d_totals && !a->d_sums && !a->d_dense) return KAS_ERR_INVALID;
     if (a->n_resources > (0x7FFFFFFFull / kMaxPoliciesPerLaunch) * kReplayThreads) return KAS_ERR_UNSUPPORTED;

@@ -39,6 +39,8 @@ def lib():
                                         C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint32,
                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.kas_oracle_replay.restype = None
+        L.kas_oracle_replay_delay.argtypes = L.kas_oracle_replay.argtypes[:-1] + [C.c_uint32, C.c_int]
+        L.kas_oracle_replay_delay.restype = None
         L.kas_oracle_trace_value.argtypes = [C.c_uint64, C.c_uint64, C.c_uint32]
         L.kas_oracle_trace_value.restype = C.c_int32
         L.kas_oracle_trace_fill.argtypes = [C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint64,
@@ -100,7 +102,13 @@ def match_counts_heads(queues, heads, threads=None):
     return counts
 
 
-def replay(llen, inprog, group_off, cur0, policies, want_dense=False, threads=None, patch_fail=None):
+MAX_STARTUP_DELAY = 64
+
+
+def replay(llen, inprog, group_off, cur0, policies, want_dense=False, threads=None, patch_fail=None,
+           startup_delay=0):
+    if not 0 <= int(startup_delay) <= MAX_STARTUP_DELAY:
+        raise ValueError('startup_delay out of range')
     llen = np.ascontiguousarray(llen, dtype=np.int32)
     T, Q = llen.shape
     mode = 0
@@ -123,13 +131,13 @@ def replay(llen, inprog, group_off, cur0, policies, want_dense=False, threads=No
     final = np.zeros((R, S), dtype=np.int32)
     dense = np.zeros((S, T, R), dtype=np.int32) if want_dense else None
     pf = None if patch_fail is None else np.ascontiguousarray(patch_fail, dtype=np.uint8).reshape(T, R)
-    lib().kas_oracle_replay(llen.ctypes.data, None if ip is None else ip.ctypes.data, mode, T, Q,
-                            None if go is None else go.ctypes.data, R,
-                            None if c0 is None else c0.ctypes.data, pol.ctypes.data, S,
-                            pod_ticks.ctypes.data, n_patches.ctypes.data, final.ctypes.data,
-                            None if dense is None else dense.ctypes.data,
-                            None if pf is None else pf.ctypes.data,
-                            threads or max_threads())
+    lib().kas_oracle_replay_delay(llen.ctypes.data, None if ip is None else ip.ctypes.data, mode, T, Q,
+                                  None if go is None else go.ctypes.data, R,
+                                  None if c0 is None else c0.ctypes.data, pol.ctypes.data, S,
+                                  pod_ticks.ctypes.data, n_patches.ctypes.data, final.ctypes.data,
+                                  None if dense is None else dense.ctypes.data,
+                                  None if pf is None else pf.ctypes.data,
+                                  int(startup_delay), threads or max_threads())
     out = dict(pod_ticks=pod_ticks, n_patches=n_patches, final=final)
     if want_dense:
         out['dense'] = dense

@@ -177,25 +177,41 @@ KAS_EXPORT int64_t kas_oracle_get_desired_pods(int64_t tally, int64_t kpp, int64
  * llen [T][Q] tick-major.  inprog_mode 0: none, 1: [Q], 2: [T][Q].
  * group_off NULL -> every queue is its own resource (R == Q).
  * policies [S][3] = kpp, min, max.  Outputs [R][S].
- * dense (optional) [S][T][R] int32 = replicas after each tick.              */
-KAS_EXPORT void kas_oracle_replay(const int32_t *llen, const int32_t *inprog, int inprog_mode,
-                                  uint32_t T, uint64_t Q,
-                                  const uint64_t *group_off, uint64_t R,
-                                  const int32_t *cur0,
-                                  const int32_t *policies, uint32_t S,
-                                  int64_t *pod_ticks, int64_t *n_patches, int32_t *final_cur,
-                                  int32_t *dense, const uint8_t *patch_fail /* [T][R] or NULL */,
-                                  int threads)
+ * dense (optional) [S][T][R] int32 = replicas after each tick.
+ *
+ * startup_delay D > 0 is the `only_running` reading of a deployment
+ * (autoscaler.py:176-177: current pods = status.available_replicas) with a
+ * modelled pod start-up time: a replica is available once it has been part of
+ * spec.replicas for D consecutive ticks, a removed replica is gone at once, so
+ *     available[t+1] = min(spec[t-D], ..., spec[t])      (spec[<0] = cur0).
+ * The controller reads `available`, decides, and patches spec.replicas when
+ * desired != available (:227) -- also when spec already holds that value.
+ * D == 0 is the plain replay (available == spec).  pod_ticks / dense / final
+ * are spec.replicas after the tick.                                          */
+#define KAS_ORACLE_MAX_DELAY 64
+KAS_EXPORT void kas_oracle_replay_delay(const int32_t *llen, const int32_t *inprog, int inprog_mode,
+                                        uint32_t T, uint64_t Q,
+                                        const uint64_t *group_off, uint64_t R,
+                                        const int32_t *cur0,
+                                        const int32_t *policies, uint32_t S,
+                                        int64_t *pod_ticks, int64_t *n_patches, int32_t *final_cur,
+                                        int32_t *dense, const uint8_t *patch_fail /* [T][R] or NULL */,
+                                        uint32_t startup_delay, int threads)
 {
+    if (startup_delay > KAS_ORACLE_MAX_DELAY) startup_delay = KAS_ORACLE_MAX_DELAY;
 #pragma omp parallel for schedule(static) num_threads(threads > 0 ? threads : 1)
     for (uint64_t r = 0; r < R; ++r) {
         uint64_t q0 = group_off ? group_off[r] : r;
         uint64_t q1 = group_off ? group_off[r + 1] : r + 1;
         for (uint32_t s = 0; s < S; ++s) {
             int64_t kpp = policies[3 * s], mn = policies[3 * s + 1], mx = policies[3 * s + 2];
-            int64_t cur = cur0 ? cur0[r] : 0;
+            int64_t spec = cur0 ? cur0[r] : 0;      /* spec.replicas / spec.parallelism */
+            int64_t avail = spec;                   /* status.available_replicas */
+            int64_t hist[KAS_ORACLE_MAX_DELAY];     /* spec of the last D ticks */
+            for (uint32_t i = 0; i < startup_delay; ++i) hist[i] = spec;
             int64_t pt = 0, np = 0;
             for (uint32_t t = 0; t < T; ++t) {
+                int64_t cur = avail;                                       /* :252 (with only_running) */
                 int64_t sum = 0;
                 for (uint64_t q = q0; q < q1; ++q) {
                     int64_t tally = llen[(uint64_t)t * Q + q];
@@ -207,16 +223,33 @@ KAS_EXPORT void kas_oracle_replay(const int32_t *llen, const int32_t *inprog, in
                 if (desired != cur) {                                      /* :227 */
                     np += 1;                                               /* the patch call is made */
                     /* ... and, if it raises, swallowed: replicas stay (:267-273) */
-                    if (!(patch_fail && patch_fail[(uint64_t)t * R + r])) cur = desired;
+                    if (!(patch_fail && patch_fail[(uint64_t)t * R + r])) spec = desired;
                 }
-                pt += cur;
-                if (dense) dense[((uint64_t)s * T + t) * R + r] = (int32_t)cur;
+                avail = spec;
+                for (uint32_t i = 0; i < startup_delay; ++i)
+                    if (hist[i] < avail) avail = hist[i];
+                if (startup_delay) hist[t % startup_delay] = spec;
+                pt += spec;
+                if (dense) dense[((uint64_t)s * T + t) * R + r] = (int32_t)spec;
             }
             pod_ticks[r * S + s] = pt;
             n_patches[r * S + s] = np;
-            final_cur[r * S + s] = (int32_t)cur;
+            final_cur[r * S + s] = (int32_t)spec;
         }
     }
+}
+
+KAS_EXPORT void kas_oracle_replay(const int32_t *llen, const int32_t *inprog, int inprog_mode,
+                                  uint32_t T, uint64_t Q,
+                                  const uint64_t *group_off, uint64_t R,
+                                  const int32_t *cur0,
+                                  const int32_t *policies, uint32_t S,
+                                  int64_t *pod_ticks, int64_t *n_patches, int32_t *final_cur,
+                                  int32_t *dense, const uint8_t *patch_fail /* [T][R] or NULL */,
+                                  int threads)
+{
+    kas_oracle_replay_delay(llen, inprog, inprog_mode, T, Q, group_off, R, cur0, policies, S,
+                            pod_ticks, n_patches, final_cur, dense, patch_fail, 0u, threads);
 }
 
 /* ---- Twin of the library's synthetic trace generator --------------------

@@ -314,18 +314,73 @@ def c1():
         tallies_default=tallies_default)
 
 
+def _run_only_running(queues, depths, kpp, mn, mx, cur0, rtype, delay, fails=None):
+    """scale() driven with the reference's only_running branch (autoscaler.py:176-177) against
+    a Kubernetes double whose available_replicas lag spec.replicas by `delay` ticks
+    (refload.StatefulKube).  For a job the reference ignores the flag (autoscaler.py:185-190)."""
+    names = queues.split(',')
+    redis = refload.StubRedis()
+    kube = refload.StatefulKube('r', rtype, cur0, startup_delay=delay)
+    s = refload.make_reference_scaler(redis, queues, ',', kube, only_running=True)
+    after, seen = [], []
+    for t, row in enumerate(depths):
+        redis.lists = dict(zip(names, row))
+        kube.fail_next_patch = bool(fails and fails[t])
+        seen.append(s.get_current_pods('ns', rtype, 'r'))
+        s.scale('ns', rtype, 'r', min_pods=mn, max_pods=mx, keys_per_pod=kpp)
+        kube.end_tick()
+        after.append(int(kube.value))
+    return dict(queues=queues, depths=depths, kpp=kpp, min=mn, max=mx, cur0=cur0, type=rtype,
+                delay=delay, fails=fails, after=after, seen=seen,
+                patches=[int(p) for p in kube.patches])
+
+
+def only_running_cases():
+    import random
+    rnd = random.Random(20261107)
+    cases = []
+    # a burst, a drain and a second burst: the start-up lag lets the target overshoot nothing
+    # but delays the hold ("never scale down to a non-zero count" compares with AVAILABLE pods)
+    ramp = [[0], [3], [6], [6], [6], [2], [2], [0], [0], [5], [5], [5], [1], [0], [0], [0]]
+    for delay in (0, 1, 2, 3, 5):
+        cases.append(_run_only_running('q', ramp, 1, 0, 8, 0, 'deployment', delay))
+        cases.append(_run_only_running('q', ramp, 2, 1, 4, 3, 'deployment', delay))
+        cases.append(_run_only_running('q', ramp, 1, 0, 8, 0, 'job', delay))
+    for _ in range(60):
+        nq = rnd.choice([1, 1, 2, 3])
+        T = rnd.randint(5, 40)
+        depths = []
+        level = 0
+        for t in range(T):
+            if rnd.random() < 0.25:
+                level = rnd.choice([0, 0, 1, 4, 9, 30])
+            depths.append([max(0, level + rnd.randint(-2, 2)) if level else 0 for _ in range(nq)])
+        fails = [rnd.random() < 0.15 for _ in range(T)] if rnd.random() < 0.3 else None
+        cases.append(_run_only_running(','.join('q%d' % i for i in range(nq)), depths,
+                                       rnd.choice([1, 1, 2, 5]), rnd.choice([0, 0, 1]),
+                                       rnd.choice([1, 4, 16]), rnd.choice([0, 0, 2, 20]),
+                                       rnd.choice(['deployment', 'deployment', 'job']),
+                                       rnd.choice([0, 1, 2, 3, 4, 7]), fails))
+    return cases
+
+
 def main():
     assert refload.available(), 'needs /root/reference'
     import logging
     logging.disable(logging.CRITICAL)
     os.makedirs(GOLD, exist_ok=True)
+    only = set(sys.argv[1:])          # fixture names to (re)write; none given: all of them
     for name, fn in [('known_answers', known_answers), ('decisions', decisions),
-                     ('scale_cases', scale_cases), ('tally_cases', tally_cases)]:
+                     ('scale_cases', scale_cases), ('tally_cases', tally_cases),
+                     ('only_running_cases', only_running_cases)]:
+        if only and name not in only:
+            continue
         with open(os.path.join(GOLD, name + '.json'), 'w') as f:
             json.dump(fn(), f, separators=(',', ':'))
         print('wrote', name)
-    c1()
-    print('wrote c1')
+    if not only or 'c1' in only:
+        c1()
+        print('wrote c1')
 
 
 if __name__ == '__main__':

@@ -198,7 +198,8 @@ def replay_resource(llen_rows: Sequence[Sequence[int]],
                     inprog_rows: Optional[Sequence[Sequence[int]]],
                     keys_per_pod: int, min_pods: int, max_pods: int,
                     cur0: int = 0,
-                    patch_fails: Optional[Sequence[bool]] = None) -> Tuple[List[int], List[int]]:
+                    patch_fails: Optional[Sequence[bool]] = None,
+                    startup_delay: int = 0) -> Tuple[List[int], List[int]]:
     """Replay one resource over T ticks with a well-behaved Kubernetes mock:
     what a tick patches (autoscaler.py:232,236) is what the next tick reads
     (autoscaler.py:179,189), and no patch is issued when desired == current
@@ -210,20 +211,35 @@ def replay_resource(llen_rows: Sequence[Sequence[int]],
     (autoscaler.py:267-273) and the resource keeps its replicas; the attempt is
     still listed.  Returns (replicas after each tick, list of values the
     patch calls carried, in order).
+
+    ``startup_delay`` D > 0 models the ``only_running`` reading of a deployment
+    (autoscaler.py:176-177, ``status.available_replicas``): a replica counts as
+    available once it has been part of ``spec.replicas`` for D consecutive ticks
+    and is gone as soon as the spec drops it, i.e. ``available[t+1] =
+    min(spec[t-D..t])`` with ``spec[<0] = cur0``.  The controller reads
+    ``available`` (autoscaler.py:252 with the flag set), and patches whenever
+    desired != available (autoscaler.py:227), also when the spec already holds
+    that value.  The returned list is ``spec.replicas`` after each tick.
     """
-    cur = cur0
+    spec = cur0
+    avail = cur0
+    hist = [cur0] * startup_delay          # spec of the last D ticks
     after, patches = [], []
     for t, row in enumerate(llen_rows):
         if inprog_rows is None:
             tallies = list(row)
         else:
             tallies = [a + b for a, b in zip(row, inprog_rows[t])]
+        cur = avail
         desired = scale_step(tallies, keys_per_pod, min_pods, max_pods, cur)
         if desired != cur:
             patches.append(desired)
             if not (patch_fails is not None and patch_fails[t]):
-                cur = desired
-        after.append(cur)
+                spec = desired
+        avail = min([spec] + hist)
+        if startup_delay:
+            hist[t % startup_delay] = spec
+        after.append(spec)
     return after, patches
 
 

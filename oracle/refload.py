@@ -124,12 +124,25 @@ class StatefulKube(object):
     (autoscaler.py:232,236 -> :179,189).  Counts are returned as strings the
     way the reference's own DummyKubernetes does (autoscaler_test.py:54-81)."""
 
-    def __init__(self, name, resource_type, replicas=0):
+    def __init__(self, name, resource_type, replicas=0, startup_delay=0):
         self.name = name
         self.resource_type = resource_type
         self.value = replicas
         self.patches = []
         self.fail_next_patch = False   # raise ApiException on the next patch call (it is still listed)
+        # availability model (only read through `only_running`, autoscaler.py:176-177): a
+        # replica is available once it has been in the spec for `startup_delay` ticks in a
+        # row; the driver calls end_tick() after every scale()
+        self.startup_delay = startup_delay
+        self.history = [replicas] * startup_delay
+        self.available = replicas
+        self.ticks = 0
+
+    def end_tick(self):
+        self.available = min([int(self.value)] + [int(h) for h in self.history])
+        if self.startup_delay:
+            self.history[self.ticks % self.startup_delay] = self.value
+        self.ticks += 1
 
     def _items(self):
         spec = _Bunch(replicas=str(self.value), parallelism=str(self.value),
@@ -139,7 +152,8 @@ class StatefulKube(object):
                    metadata=_Bunch(name=self.name + '-other'),
                    status=_Bunch(available_replicas=None)),
             _Bunch(spec=spec, metadata=_Bunch(name=self.name),
-                   status=_Bunch(available_replicas=str(self.value)))])
+                   status=_Bunch(available_replicas=str(self.available if self.startup_delay
+                                                        else self.value)))])
 
     def list_namespaced_deployment(self, namespace):
         return self._items()
@@ -162,11 +176,21 @@ class StatefulKube(object):
         return self._patch(name, namespace, body, 'parallelism')
 
 
-def make_reference_scaler(redis_client, queues, queue_delim=',', kube=None):
-    """A reference ``Autoscaler`` whose k8s clients are the given double."""
+def make_reference_scaler(redis_client, queues, queue_delim=',', kube=None, only_running=False):
+    """A reference ``Autoscaler`` whose k8s clients are the given double.
+    ``only_running``: ``scale()`` reads the current pods with the reference's own
+    ``only_running=True`` branch (autoscaler.py:176-177), which ``scale()`` itself never
+    selects (autoscaler.py:252) -- the only line of ours on that path is the flag."""
     import logging
     mod = reference_autoscaler_module()
-    scaler = mod.Autoscaler(redis_client, queues=queues, queue_delim=queue_delim)
+    cls = mod.Autoscaler
+    if only_running:
+        class OnlyRunning(mod.Autoscaler):
+            def get_current_pods(self, namespace, resource_type, name, only_running=False):
+                return mod.Autoscaler.get_current_pods(self, namespace, resource_type, name,
+                                                       only_running=True)
+        cls = OnlyRunning
+    scaler = cls(redis_client, queues=queues, queue_delim=queue_delim)
     scaler.logger.setLevel(logging.CRITICAL)
     if kube is not None:
         scaler.get_apps_v1_client = lambda: kube

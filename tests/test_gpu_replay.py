@@ -316,3 +316,63 @@ def test_failing_patch_calls(shape):
     assert (np.diff(log.off.astype(np.int64)) == want['n_patches'][:, 1]).all()
     with pytest.raises(ValueError):
         autoscaler.replay.replay_fleet(llen, pol, group_off=go, patch_fail=fail[:-1])
+
+
+def test_only_running_reference_fixture():
+    """The start-up-delay replay against what the reference's own scale() +
+    get_current_pods(only_running=True) did (tests/golden/only_running_cases.json)."""
+    import autoscaler
+    for case in helpers.golden_json('only_running_cases'):
+        names = case['queues'].split(',')
+        scaler = autoscaler.Autoscaler(None, queues=case['queues'])
+        fails = case.get('fails')
+        got = scaler.replay(np.array(case['depths'], dtype=np.int32),
+                            [(case['kpp'], case['min'], case['max'])], current_pods=case['cur0'],
+                            resource_type=case['type'], want_dense=True, patch_fail=fails,
+                            startup_delay=case['delay'])
+        assert got.dense[0, :, 0].tolist() == case['after']
+        assert int(got.n_patches[0, 0]) == len(case['patches'])
+        log = autoscaler.replay.patch_events(np.array(case['depths'], dtype=np.int32),
+                                             (case['kpp'], case['min'], case['max']),
+                                             group_off=np.array([0, len(names)], dtype=np.uint64),
+                                             cur0=np.array([case['cur0']]), resource_types=case['type'],
+                                             patch_fail=None if fails is None else np.array(fails).reshape(-1, 1),
+                                             startup_delay=case['delay'])
+        ev = log.of(0)
+        assert [int(e['to_pods']) for e in ev] == case['patches']
+        # what the controller read on the ticks it patched
+        assert [int(e['from_pods']) for e in ev] == [case['seen'][int(e['tick'])] for e in ev]
+
+
+@pytest.mark.parametrize('shape', ['identity', 'grouped', 'identity_u16'])
+@pytest.mark.parametrize('delay', [1, 3, 16])
+def test_startup_delay_fleets_vs_oracle(shape, delay):
+    import autoscaler
+    from oracle import coracle
+    rng = np.random.default_rng(hash((shape, delay)) % (2 ** 32))
+    T, Q = 90, 6000
+    llen, go = helpers.random_fleet(rng, T, Q, grouped=(shape == 'grouped'))
+    R = Q if go is None else len(go) - 1
+    cur0 = rng.integers(0, 9, size=R).astype(np.int32)
+    fail = rng.random((T, R)) < 0.05
+    pols = [(1, 0, 1), (2, 0, 8), (1, 1, 4), (5, 0, 64), (3, 9, 5), (-2, 0, 6)]
+    want = coracle.replay(llen, None, go, cur0, pols, want_dense=True, patch_fail=fail, startup_delay=delay)
+    trace = llen.astype(np.uint16) if shape == 'identity_u16' else llen
+    if shape == 'identity_u16':
+        want = coracle.replay(trace.astype(np.int32), None, go, cur0, pols, want_dense=True,
+                              patch_fail=fail, startup_delay=delay)
+    got = autoscaler.replay.replay_fleet(trace, pols, group_off=go, cur0=cur0, want_dense=True,
+                                         patch_fail=fail, startup_delay=delay)
+    assert (got.dense == want['dense']).all()
+    assert (got.pod_ticks == want['pod_ticks']).all()
+    assert (got.n_patches == want['n_patches']).all()
+    assert (got.final == want['final']).all()
+    assert (got.sums[:, 1] == want['n_patches'].sum(0)).all()
+    # a job ignores the delay (autoscaler.py:185-190)
+    job = autoscaler.replay.replay_fleet(trace, pols[:2], group_off=go, cur0=cur0, resource_type='job',
+                                         startup_delay=delay)
+    plain = autoscaler.replay.replay_fleet(trace, pols[:2], group_off=go, cur0=cur0)
+    assert (job.pod_ticks == plain.pod_ticks).all() and (job.n_patches == plain.n_patches).all()
+    log = autoscaler.replay.patch_events(trace, pols[1], group_off=go, cur0=cur0, patch_fail=fail,
+                                         startup_delay=delay)
+    assert (np.diff(log.off.astype(np.int64)) == want['n_patches'][:, 1]).all()

@@ -67,6 +67,30 @@ def test_scale_cases():
             assert n['dense'][0, :, 0].tolist() == case['after']
 
 
+def test_only_running_cases():
+    """The start-up-delay model of `only_running` (autoscaler.py:176-177): the reference's
+    own scale() + get_current_pods(only_running=True) against a Kubernetes double whose
+    available_replicas lag the spec; a job ignores the flag (autoscaler.py:185-190)."""
+    cases = helpers.golden_json('only_running_cases')
+    assert len(cases) >= 60 and any(c['delay'] >= 3 and c['fails'] for c in cases)
+    for case in cases:
+        delay = case['delay'] if case['type'] == 'deployment' else 0
+        fails = case.get('fails')
+        after, patches = oracle.replay_resource(case['depths'], None, case['kpp'], case['min'],
+                                                case['max'], case['cur0'], fails, startup_delay=delay)
+        assert after == case['after'] and patches == case['patches']
+        nq = len(case['depths'][0])
+        res = coracle.replay(np.array(case['depths'], dtype=np.int32), None,
+                             np.array([0, nq], dtype=np.uint64), [case['cur0']],
+                             [(case['kpp'], case['min'], case['max'])], want_dense=True,
+                             patch_fail=None if fails is None else np.array(fails).reshape(-1, 1),
+                             startup_delay=delay)
+        assert res['dense'][0, :, 0].tolist() == case['after']
+        assert res['n_patches'][0, 0] == len(case['patches'])
+        assert res['pod_ticks'][0, 0] == sum(case['after'])
+        assert res['final'][0, 0] == case['after'][-1]
+
+
 def test_tally_cases():
     for case in helpers.golden_json('tally_cases'):
         names = list(oracle.parse_queues(case['queues'], case['delim']))
