@@ -384,10 +384,23 @@ __device__ __forceinline__ void bulk_copy_g2s(void *smem_dst, const void *gmem_s
                    "r"((uint32_t)__cvta_generic_to_shared(bar)) : "memory");
 }
 
-template <typename E, bool TICKIP, int MODE, bool NARROW>
+// How the sweep kernel keeps its per-(resource, policy) state, chosen by the host:
+//   kAccWide    pod-ticks in 64 bits every tick (any values)
+//   kAccNarrow  32-bit pod-tick sums per tile (max_pods < kSweepNarrowBound, no cur0)
+//   kAccPacked  two resources per register, 16 bits each: current pods, and per tile the
+//               patches and pod-ticks (0 <= min_pods, max_pods <= kSweepPackedMaxPods, no
+//               cur0, keys_per_pod <= 2^14); a batch of ticks with a count >= 2^14 is
+//               replayed unpacked.  Every form gives the same integers.
+enum SweepAcc { kAccWide = 0, kAccNarrow = 1, kAccPacked = 2 };
+constexpr int32_t kSweepPackedMaxPods = 1023;           // x 64 ticks of a tile stays below 2^16
+constexpr uint32_t kSweepPackedTallyTerm = 1u << 14;    // both terms below: the quotient fits 15 bits
+
+template <typename E, bool TICKIP, int MODE, int ACC>
 __global__ void __launch_bounds__(32 * kSweepMaxWarps, 1)
 replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
     constexpr int SP = kSweepSP, VEC = 4;
+    constexpr bool NARROW = ACC == kAccNarrow;
+    constexpr bool PACKED = ACC == kAccPacked;
     constexpr int kEPP = 16 / (int)sizeof(E);                 // trace elements per 16-byte piece
     constexpr int kGroupPieces = kSweepCols / kEPP;           // pieces per tick and column group
     extern __shared__ int4 sweep_smem[];            // [TICKIP ? 2 : 1][kSweepStages][ticks][groups][kGroupPieces] int4
@@ -447,6 +460,18 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
     for (int s = 0; s < SP; ++s)
 #pragma unroll
         for (int v = 0; v < VEC; ++v) pa[s][v] = 0u;
+    // PACKED: resources (0,1) and (2,3) of this lane share a register, low and high half.
+    // cur2 is THE current-pods state of the kernel (cur[][] only lives inside a batch that is
+    // replayed unpacked and after the last tile); np2 / pa2 are emptied once per tile.
+    uint32_t cur2[SP][VEC / 2], np2[SP][VEC / 2], pa2[SP][VEC / 2], mx2[SP], mn2[SP];
+#pragma unroll
+    for (int s = 0; s < SP; ++s) {
+        mx2[s] = (uint32_t)pol[s].mx * 0x00010001u;
+        mn2[s] = (uint32_t)pol[s].mn * 0x00010001u;
+#pragma unroll
+        for (int p = 0; p < VEC / 2; ++p) { cur2[s][p] = 0u; np2[s][p] = 0u; pa2[s][p] = 0u; }
+    }
+    const uint32_t add2 = keep.add * 0x00010001u;
 
     const uint32_t n_tiles = (T + tile_ticks - 1) / tile_ticks;
 #if KAS_SWEEP_TMA
@@ -532,8 +557,9 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
             };
             // G ticks at a time: their rows are read from shared memory first, one sign
             // test picks the arithmetic for all of them, then the recurrences run
-            auto ticks = [&](uint32_t t, auto gtag) {
+            auto ticks = [&](uint32_t t, auto gtag, auto densetag) {
                 constexpr int G = decltype(gtag)::value;
+                constexpr bool DENSE = decltype(densetag)::value;   // chosen per tile, so the tick code has no branch
                 int32_t l[G][VEC], ip[G][VEC];
                 int32_t any = ipq_sign;
 #pragma unroll
@@ -541,7 +567,7 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
                     read4(tl + (t + g) * row_elems, l[g]);
                     if (TICKIP) {
                         read4(ti + (t + g) * row_elems, ip[g]);
-                        if constexpr (sizeof(E) == 4) {
+                        if constexpr (sizeof(E) == 4 || PACKED) {
 #pragma unroll
                             for (int v = 0; v < VEC; ++v) any |= ip[g][v];
                         }
@@ -549,7 +575,7 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
 #pragma unroll
                         for (int v = 0; v < VEC; ++v) ip[g][v] = ipq[v];
                     }
-                    if constexpr (sizeof(E) == 4) {   // a uint16 element is neither negative nor >= 2^16
+                    if constexpr (sizeof(E) == 4 || PACKED) {   // a uint16 element is neither negative nor >= 2^16
 #pragma unroll
                         for (int v = 0; v < VEC; ++v) any |= l[g][v];
                     }
@@ -586,36 +612,115 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
                                 cur[s][v] = want;
                                 // (issuing these two adds on the FMA pipe instead measured 1-8 % slower)
                                 if constexpr (NARROW && FAST) pa[s][v] += (uint32_t)want;
-                                else add_pod_ticks(pt[s][v], want, one);
+                                else add_pod_ticks(pt[s][v], want, one);   // also a PACKED kernel's unpacked batch
                             }
-                            if (dense && live[s]) {
+                            if (DENSE && live[s]) {
                                 int32_t *o = P.dense + ((uint64_t)P.pol_index[pbase + s] * T + t0 + t + g) * P.R + r0;
                                 *reinterpret_cast<int4 *>(o) = make_int4(cur[s][0], cur[s][1], cur[s][2], cur[s][3]);
                             }
                         }
                     }
                 };
+                // PACKED: two resources per instruction (min / max3 / add on 16-bit halves, sm_100's
+                // VIMNMX.U16x2, VIMNMX3.S16x2, VIADDMNMX.U16x2, VIADD.16x2).  Per pair of resources the
+                // pair of policies shares the quotients, packed q2, and the keep factors as a mask km2
+                // (0xFFFF where keep == 1); per policy: min with max_pods, the three-input maximum with
+                // min_pods and the kept current pods, and the two sums of the tile.
+                auto run_packed = [&]() {
+#pragma unroll
+                    for (int g = 0; g < G; ++g) {
+                        uint32_t q2[VEC / 2], km2[VEC / 2];
+#pragma unroll
+                        for (int p = 0; p < VEC / 2; ++p) {
+                            const uint32_t qa = quotient_small((uint32_t)l[g][2 * p] + (uint32_t)ip[g][2 * p] + 1u, pol[0]);
+                            const uint32_t qb = quotient_small((uint32_t)l[g][2 * p + 1] + (uint32_t)ip[g][2 * p + 1] + 1u, pol[0]);
+                            q2[p] = __byte_perm(qa, qb, 0x5410);                       // both below 2^15
+                            km2[p] = __viaddmin_u16x2(q2[p], add2, 0x00010001u) * 0xFFFFu;
+                        }
+#pragma unroll
+                        for (int s = 0; s < SP; ++s) {
+#pragma unroll
+                            for (int p = 0; p < VEC / 2; ++p) {
+                                const uint32_t c2 = cur2[s][p];
+                                const uint32_t w2 = __vimax3_s16x2(__vminu2(q2[p], mx2[s]), mn2[s], c2 & km2[p]);   // :255-259
+                                np2[s][p] = __vadd2(np2[s][p], __vminu2(w2 ^ c2, 0x00010001u));                  // :227
+                                pa2[s][p] = __vadd2(pa2[s][p], w2);
+                                cur2[s][p] = w2;
+                            }
+                            if (DENSE && live[s]) {
+                                int32_t *o = P.dense + ((uint64_t)P.pol_index[pbase + s] * T + t0 + t + g) * P.R + r0;
+                                *reinterpret_cast<int4 *>(o) = make_int4((int32_t)(cur2[s][0] & 0xFFFFu), (int32_t)(cur2[s][0] >> 16),
+                                                                         (int32_t)(cur2[s][1] & 0xFFFFu), (int32_t)(cur2[s][1] >> 16));
+                            }
+                        }
+                    }
+                };
+                if constexpr (PACKED) {
+                    if (__all_sync(working, (uint32_t)any < kSweepPackedTallyTerm)) {
+                        run_packed();
+                        return;
+                    }
+                    // a count too large (or negative): this batch unpacked
+#pragma unroll
+                    for (int s = 0; s < SP; ++s)
+#pragma unroll
+                        for (int p = 0; p < VEC / 2; ++p) {
+                            cur[s][2 * p] = (int32_t)(cur2[s][p] & 0xFFFFu);
+                            cur[s][2 * p + 1] = (int32_t)(cur2[s][p] >> 16);
+                        }
+                }
                 // every count of the batch below 2^16 (and keys_per_pod <= 2^14): short quotient
                 // (a whole-warp choice, so that one large count does not make the warp run both forms)
                 if (MODE != kGeneric && small_kpp && __all_sync(working, (uint32_t)any < kSmallTallyTerm))
                     run(std::true_type{}, std::true_type{});
                 else if (MODE != kGeneric && any >= 0) run(std::true_type{}, std::false_type{});
                 else run(std::false_type{}, std::false_type{});
+                if constexpr (PACKED) {
+#pragma unroll
+                    for (int s = 0; s < SP; ++s)
+#pragma unroll
+                        for (int p = 0; p < VEC / 2; ++p)
+                            cur2[s][p] = (uint32_t)cur[s][2 * p] | ((uint32_t)cur[s][2 * p + 1] << 16);
+                }
             };
             uint32_t t = 0;
-            for (; t + 4 <= nt; t += 4) ticks(t, std::integral_constant<int, 4>{});
-            for (; t < nt; ++t) ticks(t, std::integral_constant<int, 1>{});
+            if (dense) {
+                for (; t + 4 <= nt; t += 4) ticks(t, std::integral_constant<int, 4>{}, std::true_type{});
+                for (; t < nt; ++t) ticks(t, std::integral_constant<int, 1>{}, std::true_type{});
+            } else {
+                for (; t + 4 <= nt; t += 4) ticks(t, std::integral_constant<int, 4>{}, std::false_type{});
+                for (; t < nt; ++t) ticks(t, std::integral_constant<int, 1>{}, std::false_type{});
+            }
             if constexpr (NARROW) {
 #pragma unroll
                 for (int s = 0; s < SP; ++s)
 #pragma unroll
                     for (int v = 0; v < VEC; ++v) { pt[s][v] += pa[s][v]; pa[s][v] = 0u; }
             }
+            if constexpr (PACKED) {
+#pragma unroll
+                for (int s = 0; s < SP; ++s)
+#pragma unroll
+                    for (int p = 0; p < VEC / 2; ++p) {
+                        pt[s][2 * p] += pa2[s][p] & 0xFFFFu;  pt[s][2 * p + 1] += pa2[s][p] >> 16;
+                        np[s][2 * p] += np2[s][p] & 0xFFFFu;  np[s][2 * p + 1] += np2[s][p] >> 16;
+                        pa2[s][p] = 0u; np2[s][p] = 0u;
+                    }
+            }
         }
     }
 #if !KAS_SWEEP_TMA
     cp_async_wait<0>();
 #endif
+    if constexpr (PACKED) {
+#pragma unroll
+        for (int s = 0; s < SP; ++s)
+#pragma unroll
+            for (int p = 0; p < VEC / 2; ++p) {
+                cur[s][2 * p] = (int32_t)(cur2[s][p] & 0xFFFFu);
+                cur[s][2 * p + 1] = (int32_t)(cur2[s][p] >> 16);
+            }
+    }
 
     if (valid && P.totals) {
 #pragma unroll
@@ -808,25 +913,32 @@ static int launch_sweep(const ReplayParams &P, int mode, cudaStream_t stream) {
     const uint64_t cols_per_block = (uint64_t)groups * kSweepCols;
     const unsigned grid = (unsigned)((P.R + cols_per_block - 1) / cols_per_block);
     const size_t smem = (size_t)(tickip ? 2 : 1) * kSweepStages * kSweepTileRows * kSweepCols * sizeof(E);
-#define KAS_LAUNCH_SWEEP(TI, MD, NW)                                                               \
+#define KAS_LAUNCH_SWEEP(TI, MD, AC)                                                               \
     do {                                                                                           \
-        auto kern = replay_sweep_kernel<E, TI, MD, NW>;                                            \
+        auto kern = replay_sweep_kernel<E, TI, MD, AC>;                                            \
         /* dynamic tiles + the static mbarriers can pass the 48 KB default */                      \
         KAS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
                                           (int)smem));                                             \
         kern<<<grid, 32 * warps, smem, stream>>>(P);                                               \
     } while (0)
-    // 32-bit pod-tick partial sums when no decision can reach kSweepNarrowBound
-    bool narrow = mode != kGeneric && P.cur0 == nullptr;
-    for (uint32_t s = 0; s < P.pol_count; ++s) narrow = narrow && P.pol[s].mx < kSweepNarrowBound;
-    if (mode != kGeneric) {
-        if (narrow) {
-            if (tickip) KAS_LAUNCH_SWEEP(true, kSimple, true); else KAS_LAUNCH_SWEEP(false, kSimple, true);
-        } else {
-            if (tickip) KAS_LAUNCH_SWEEP(true, kSimple, false); else KAS_LAUNCH_SWEEP(false, kSimple, false);
+    // state width (SweepAcc): what the policies of this launch and the absence of cur0 allow
+    int acc = kAccWide;
+    if (mode != kGeneric && P.cur0 == nullptr) {
+        bool narrow = true, packed = true;
+        for (uint32_t s = 0; s < P.pol_count; ++s) {
+            narrow = narrow && P.pol[s].mx < kSweepNarrowBound;
+            packed = packed && P.pol[s].mn >= 0 && P.pol[s].mx <= kSweepPackedMaxPods && P.pol[s].m32 != 0u;
         }
+        acc = packed ? kAccPacked : (narrow ? kAccNarrow : kAccWide);
+    }
+    if (mode == kGeneric) {
+        if (tickip) KAS_LAUNCH_SWEEP(true, kGeneric, kAccWide); else KAS_LAUNCH_SWEEP(false, kGeneric, kAccWide);
+    } else if (acc == kAccPacked) {
+        if (tickip) KAS_LAUNCH_SWEEP(true, kSimple, kAccPacked); else KAS_LAUNCH_SWEEP(false, kSimple, kAccPacked);
+    } else if (acc == kAccNarrow) {
+        if (tickip) KAS_LAUNCH_SWEEP(true, kSimple, kAccNarrow); else KAS_LAUNCH_SWEEP(false, kSimple, kAccNarrow);
     } else {
-        if (tickip) KAS_LAUNCH_SWEEP(true, kGeneric, false); else KAS_LAUNCH_SWEEP(false, kGeneric, false);
+        if (tickip) KAS_LAUNCH_SWEEP(true, kSimple, kAccWide); else KAS_LAUNCH_SWEEP(false, kSimple, kAccWide);
     }
 #undef KAS_LAUNCH_SWEEP
     return KAS_OK;

@@ -26,6 +26,11 @@ __global__ void __launch_bounds__(512, 1) k(int *out, int a, int b, int one, lon
                              w[i] = (long long)a * (long long)one + w[i]; }                        // 2 wide
             if (KIND == 6) { x[i] = max(x[i], a); x[i] = min(x[i], b); x[i] = x[i] * a + b; }       // 2 alu + 1 fma
             if (KIND == 7) { x[i] = max(x[i], a); x[i] = x[i] * a + b; x[i] = x[i] * b + a; }       // 1 alu + 2 fma
+            if (KIND == 8) { x[i] = __vmins2(x[i], a); x[i] = __vmaxs2(x[i], b); }                  // VIMNMX.S16x2
+            if (KIND == 9) { x[i] = __vimax3_s16x2(x[i], a, b); x[i] = __vimin3_s16x2(x[i], b, one); }
+            if (KIND == 10) { x[i] = __vadd2(x[i], a); x[i] = __vadd2(x[i], b); }                   // VIADD.16x2
+            if (KIND == 11) { x[i] = __viaddmin_u16x2(x[i], a, b); x[i] = __viaddmax_u16x2(x[i], b, one); }
+            if (KIND == 12) { x[i] = __vminu2(x[i], a); x[i] = x[i] ^ b; }                          // VIMNMX.U16x2 + LOP3
         }
     }
     const long long t1 = clock64();
@@ -59,6 +64,11 @@ int main() {
         run<5>("IMAD.WIDE x2", 2, warps);
         run<6>("2 VIMNMX + 1 IMAD", 3, warps);
         run<7>("1 VIMNMX + 2 IMAD", 3, warps);
+        run<8>("VIMNMX.S16x2 x2", 2, warps);
+        run<9>("VIMNMX3.S16x2 x2", 2, warps);
+        run<10>("VIADD.16x2 x2", 2, warps);
+        run<11>("VIADDMNMX.U16x2 x2", 2, warps);
+        run<12>("VIMNMX.U16x2 + LOP3", 2, warps);
     }
     return 0;
 }

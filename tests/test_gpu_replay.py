@@ -151,6 +151,61 @@ def test_sweep_pairing_and_pod_tick_widths(width, dtype, ipmode):
         assert int(got.dense.max()) == 2 ** 24 - 1 or dtype == 'uint16'
 
 
+PACKABLE = [(1, 0, 1), (1, 0, 0), (1, 1, 1), (2, 0, 3), (2, 0, 1023), (2, 2, 5), (3, 0, 0), (3, 0, 7), (3, 1, 7),
+            (5, 0, 1023), (5, 1023, 1023), (7, 0, 9), (7, 0, 9), (7, 0, 11), (9, 4, 4), (16384, 0, 3), (1, 0, 1023)]
+
+
+@pytest.mark.parametrize('data', ['small', 'sporadic_big', 'negatives', 'saturated'])
+@pytest.mark.parametrize('dtype', ['int32', 'uint16'])
+@pytest.mark.parametrize('ipmode', [0, 1, 2])
+def test_sweep_packed_state(data, dtype, ipmode):
+    """The sweep kernel's packed form (two resources per register, 16 bits each; policies with
+    0 <= min, max <= 1023, keys_per_pod <= 2^14, no cur0): all-small counts, batches that leave
+    the packed form because of a large or negative count and come back, and max_pods = 1023 held
+    for whole tiles (the 16-bit pod-tick sum of a tile at 64 x 1023)."""
+    if dtype == 'uint16' and data == 'negatives':
+        pytest.skip('no negative uint16')
+    import autoscaler
+    from oracle import coracle
+    rng = np.random.default_rng(hash((data, dtype, ipmode)) % (2 ** 32))
+    T, Q = 200, 8192
+    hi = 2 ** 16 - 1 if dtype == 'uint16' else 2 ** 31 - 1
+    llen = rng.integers(0, 60, size=(T, Q)).astype(np.int64)
+    llen[rng.random(llen.shape) < 0.3] = 0
+    llen[:, rng.random(Q) < 0.1] += 16000            # right below / above the packed limit of 2^14
+    if data == 'sporadic_big':
+        llen[rng.random(llen.shape) < 0.002] = hi
+        llen[rng.random(llen.shape) < 0.002] = 16384
+    if data == 'negatives':
+        llen[rng.random(llen.shape) < 0.002] = -rng.integers(1, 50)
+    if data == 'saturated':
+        llen[:, rng.random(Q) < 0.5] = 16383
+    inprog = None
+    if ipmode == 1:
+        inprog = rng.integers(0, 5, size=Q).astype(np.int64)
+        inprog[rng.random(Q) < 0.01] = 70000
+    elif ipmode == 2:
+        inprog = rng.integers(0, 9, size=(T, Q)).astype(np.int64)
+    np_t = np.uint16 if dtype == 'uint16' else np.int32
+    llen = np.minimum(llen, hi)
+    want = coracle.replay(llen.astype(np.int32), None if inprog is None else inprog.astype(np.int32),
+                          None, None, PACKABLE, want_dense=True)
+    ip_dev = None if inprog is None else (inprog.astype(np_t) if ipmode == 2 else inprog.astype(np.int32))
+    got = autoscaler.replay.replay_fleet(llen.astype(np_t), PACKABLE, inprog=ip_dev, want_dense=True)
+    assert (got.dense == want['dense']).all()
+    assert (got.pod_ticks == want['pod_ticks']).all()
+    assert (got.n_patches == want['n_patches']).all()
+    assert (got.final == want['final']).all()
+    assert (got.sums[:, 0] == want['pod_ticks'].sum(0)).all()
+    assert (got.sums[:, 1] == want['n_patches'].sum(0)).all()
+    # and without the dense output (the other instance of the tick code)
+    got2 = autoscaler.replay.replay_fleet(llen.astype(np_t), PACKABLE, inprog=ip_dev)
+    assert (got2.pod_ticks == want['pod_ticks']).all() and (got2.n_patches == want['n_patches']).all()
+    assert (got2.final == want['final']).all()
+    if data == 'saturated':
+        assert int(want['dense'].max()) == 1023
+
+
 def test_synth_trace_twin():
     from autoscaler import engine
     from oracle import coracle
