@@ -35,7 +35,7 @@ namespace kas {
 #define KAS_MATCH_THREADS 1024   // one big block per SM: the table is staged once per SM (narrow records)
 #endif
 constexpr uint32_t kNoQueue = 0xFFFFFFFFu;
-constexpr size_t kMaxMatchSmem = 200 * 1024;
+constexpr size_t kMaxMatchSmem = 226 * 1024;   // of the 227 KB a block can have
 
 // ':' detector, cheap form: 0x80 in every byte of w that equals 0x3A, and possibly
 // in bytes ABOVE such a byte of the same word (borrow).  The lowest flag of a word
@@ -71,6 +71,9 @@ struct MatchCfg {
     using mask_t = typename std::conditional<(kRows <= 32), uint32_t, uint64_t>::type;   // one bit per colon position
     // a deferred walk: region words + the position already dealt with, padded to 128-bit rows
     static constexpr int kItemWords = (kRW + 1 + 3) / 4 * 4;
+    // Shared-memory copies of every mask row, one per lane of a quarter warp (the unit a 128-bit
+    // shared load is served in): lanes that need different rows then never meet in a bank.
+    static constexpr int kMaskCopies = NCHUNK <= 2 ? 8 : 1;
     static_assert(kEW % 4 == 0, "entry rows must be 128-bit multiples");
 };
 // per warp: at most 31 waiting + 32 pushed per record parked in one go.  JOINT: the two
@@ -79,8 +82,8 @@ struct MatchCfg {
 constexpr int queue_items(bool joint) { return joint ? 32 + 32 * KAS_MATCH_U : 64; }
 
 struct MatchSmem {
-    const uint32_t *masks;    // [kRows][kRWP]
-    const uint32_t *entries;  // [n_slots][kEW]
+    const uint32_t *masks;    // [kRWP / 4][kRows][kMaskCopies] x 128 bits
+    const uint32_t *entries;  // [kEW / 4][n_slots][entry copies] x 128 bits
     uint32_t *hist;           // [n_prefix]
     uint32_t *queue;          // this warp's [queue_items(JOINT)][kItemWords]
 };
@@ -97,6 +100,7 @@ struct Matcher {
                          IW = Cfg::kItemWords;
     MatchSmem sm;
     uint32_t seed, slot_shift, lane, lanemask_lt, one;
+    uint32_t n_slots, ecopy_shift, ecopy;   // entry rows: 2^ecopy_shift copies, this lane reads copy `ecopy`
     bool two_slot;
     mask_t len_mask;
     uint32_t waiting;   // deferred walks in this warp's queue (warp-uniform)
@@ -142,10 +146,11 @@ struct Matcher {
     // a virtual entry) and whether a longer entry continues it.
     __device__ __forceinline__ bool lookup(const uint32_t (&r)[RW], int L, uint32_t &qid, bool &ext) const {
         uint32_t m[RWP];
-        const uint4 *mrow = reinterpret_cast<const uint4 *>(sm.masks + (uint32_t)L * RWP);
+        const uint4 *mrow = reinterpret_cast<const uint4 *>(sm.masks) +
+                            (uint32_t)L * Cfg::kMaskCopies + (lane & (Cfg::kMaskCopies - 1));
 #pragma unroll
         for (int j = 0; j < RWP / 4; ++j) {
-            const uint4 v = mrow[j];
+            const uint4 v = mrow[j * (Cfg::kRows * Cfg::kMaskCopies)];
             m[4 * j] = v.x; m[4 * j + 1] = v.y; m[4 * j + 2] = v.z; m[4 * j + 3] = v.w;
         }
         uint32_t h = 0;
@@ -157,10 +162,10 @@ struct Matcher {
         const uint32_t tag = hash_finish(h, (uint32_t)L + 1u, seed);
         uint32_t w[EW];
         auto fetch = [&](uint32_t slot) {
-            const uint4 *e = reinterpret_cast<const uint4 *>(sm.entries + slot * EW);
+            const uint4 *e = reinterpret_cast<const uint4 *>(sm.entries) + ((slot << ecopy_shift) + ecopy);
 #pragma unroll
             for (int j = 0; j < EW / 4; ++j) {
-                const uint4 v = e[j];
+                const uint4 v = e[(uint32_t)j * (n_slots << ecopy_shift)];
                 w[4 * j] = v.x; w[4 * j + 1] = v.y; w[4 * j + 2] = v.z; w[4 * j + 3] = v.w;
             }
             uint32_t diff = 0;
@@ -313,7 +318,8 @@ template <int NCHUNK, bool WIDE, bool JOINT>
 __global__ void __launch_bounds__(MatchCfg<NCHUNK>::kThreads, MatchCfg<NCHUNK>::kMinBlocks)
 match_count_kernel(const uint8_t *__restrict__ heads, uint64_t n_keys,
                    const uint32_t *__restrict__ tbl, uint32_t n_prefix, uint32_t n_slots,
-                   uint32_t log2_slots, uint32_t one, unsigned long long *__restrict__ counts) {
+                   uint32_t log2_slots, uint32_t ecopy_shift, uint32_t one,
+                   unsigned long long *__restrict__ counts) {
     using Cfg = MatchCfg<NCHUNK>;
     constexpr int XW = Cfg::kRecWords;
     constexpr int U = Cfg::kKeysPerThread;
@@ -328,11 +334,28 @@ match_count_kernel(const uint8_t *__restrict__ heads, uint64_t n_keys,
             for (uint32_t i = threadIdx.x; i < n_prefix; i += blockDim.x) counts[i] = ~0ull;
         return;
     }
-    const uint32_t image_words = Cfg::kRows * Cfg::kRWP + n_slots * Cfg::kEW;
-    for (uint32_t i = threadIdx.x; i < image_words; i += blockDim.x) smem[i] = tbl[kTableHeaderWords + i];
+    // Stage the table image ([kRows][kRWP] mask rows, [n_slots][kEW] entry rows) in the layout
+    // the lookups read: 128-bit pieces, piece-major, every row in several copies.
+    const uint32_t mask_words = Cfg::kRows * Cfg::kRWP * Cfg::kMaskCopies;
+    const uint32_t entry_words = (n_slots * Cfg::kEW) << ecopy_shift;
+    const uint32_t image_words = mask_words + entry_words;
+    for (uint32_t i = threadIdx.x; i < Cfg::kRows * Cfg::kRWP; i += blockDim.x) {
+        const uint32_t row = i / Cfg::kRWP, k = i % Cfg::kRWP, v = tbl[kTableHeaderWords + i];
+        uint32_t *dst = smem + (((k / 4) * Cfg::kRows + row) * Cfg::kMaskCopies) * 4 + (k % 4);
+        for (int c = 0; c < Cfg::kMaskCopies; ++c) dst[4 * c] = v;
+    }
+    for (uint32_t i = threadIdx.x; i < n_slots * Cfg::kEW; i += blockDim.x) {
+        const uint32_t slot = i / Cfg::kEW, k = i % Cfg::kEW;
+        const uint32_t v = tbl[kTableHeaderWords + Cfg::kRows * Cfg::kRWP + i];
+        uint32_t *dst = smem + mask_words + ((((k / 4) * n_slots + slot) << ecopy_shift) * 4) + (k % 4);
+        for (uint32_t c = 0; c < (1u << ecopy_shift); ++c) dst[4 * c] = v;
+    }
     Matcher<NCHUNK> mt;
     mt.sm.masks = smem;
-    mt.sm.entries = smem + Cfg::kRows * Cfg::kRWP;
+    mt.sm.entries = smem + mask_words;
+    mt.n_slots = n_slots;
+    mt.ecopy_shift = ecopy_shift;
+    mt.ecopy = threadIdx.x & ((1u << ecopy_shift) - 1u);
     mt.sm.hist = smem + image_words;
     mt.sm.queue = smem + image_words + ((n_prefix + 3u) & ~3u) +
                   (threadIdx.x >> 5) * (queue_items(JOINT) * Cfg::kItemWords);
@@ -443,24 +466,34 @@ static uint32_t item_words(uint32_t rec_bytes) {
     return (region_words(rec_bytes) + 1 + 3) / 4 * 4;
 }
 
-static size_t match_smem_bytes(uint32_t n_prefix, uint32_t rec_bytes, bool joint = false) {
+static size_t match_smem_bytes(uint32_t n_prefix, uint32_t rec_bytes, bool joint = false,
+                               uint32_t ecopy_shift = 0) {
     const size_t threads = rec_bytes <= 32 ? KAS_MATCH_THREADS : 256;   // MatchCfg<>::kThreads
     const size_t queues = (threads / 32) * queue_items(joint) * item_words(rec_bytes);
-    return (image_words(n_prefix, rec_bytes) + ((n_prefix + 3u) & ~3u) + queues) * sizeof(uint32_t);
+    const size_t mask_copies = rec_bytes <= 32 ? 8 : 1;                  // MatchCfg<>::kMaskCopies
+    const size_t masks = (size_t)length_rows(rec_bytes) * region_words_padded(rec_bytes) * mask_copies;
+    const size_t entries = ((size_t)slots_for(n_prefix) * entry_words(rec_bytes)) << ecopy_shift;
+    return (masks + entries + ((n_prefix + 3u) & ~3u) + queues) * sizeof(uint32_t);
 }
 
 template <int NCHUNK, bool WIDE, bool JOINT = false>
 static int launch_match(const void *d_heads, uint64_t n_keys, const void *d_tbl, uint32_t n_prefix,
                         uint64_t *d_counts, cudaStream_t stream) {
     const uint32_t rec_bytes = 16 * NCHUNK;
+    // Shared memory beside the table goes, in this order, to copies of the entry rows (8, 4
+    // or 2: bank conflicts of the lookups) and to the larger queue of joint parking.
+    // (Wide records run three 256-thread blocks per SM: copies only while that stays so.)
+    const size_t extras_limit = NCHUNK <= 2 ? kMaxMatchSmem : 72 * 1024;
+    uint32_t ecopy_shift = 3;
+    while (ecopy_shift > 0 && match_smem_bytes(n_prefix, rec_bytes, JOINT, ecopy_shift) > extras_limit) --ecopy_shift;
     if constexpr (!JOINT && NCHUNK <= 2) {   // two records per step: park them together if it fits
-        if (match_smem_bytes(n_prefix, rec_bytes, true) <= kMaxMatchSmem)
+        if (match_smem_bytes(n_prefix, rec_bytes, true, ecopy_shift) <= extras_limit)
             return launch_match<NCHUNK, WIDE, true>(d_heads, n_keys, d_tbl, n_prefix, d_counts, stream);
     }
     const uint32_t n_slots = slots_for(n_prefix);
     uint32_t log2_slots = 0;
     while ((1u << log2_slots) < n_slots) ++log2_slots;
-    const size_t smem = match_smem_bytes(n_prefix, rec_bytes, JOINT);
+    const size_t smem = match_smem_bytes(n_prefix, rec_bytes, JOINT, ecopy_shift);
     if (smem > kMaxMatchSmem) return KAS_ERR_UNSUPPORTED;
     auto kern = match_count_kernel<NCHUNK, WIDE, JOINT>;
     if (smem > 48 * 1024)
@@ -477,7 +510,7 @@ static int launch_match(const void *d_heads, uint64_t n_keys, const void *d_tbl,
     if (grid == 0) grid = 1;
     kern<<<(unsigned)grid, MatchCfg<NCHUNK>::kThreads, smem, stream>>>(
         static_cast<const uint8_t *>(d_heads), n_keys, static_cast<const uint32_t *>(d_tbl),
-        n_prefix, n_slots, log2_slots, 1u, reinterpret_cast<unsigned long long *>(d_counts));
+        n_prefix, n_slots, log2_slots, ecopy_shift, 1u, reinterpret_cast<unsigned long long *>(d_counts));
     KAS_CUDA_TRY(cudaGetLastError());
     return KAS_OK;
 }
