@@ -38,6 +38,14 @@ __device__ __forceinline__ uint4 ldg_nc_128(const void *p) {
                  : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
     return r;
 }
+// 128-bit shared-memory load at a 32-bit shared address (the address arithmetic stays 32-bit
+// and the window base is not re-derived at every use).
+__device__ __forceinline__ uint4 lds_128(uint32_t saddr) {
+    uint4 r;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(saddr));
+    return r;
+}
 // sm_100 256-bit load (LDG.E.256): one whole 32-byte sector per thread.
 __device__ __forceinline__ void ldg_stream_256(const void *p, uint32_t (&r)[8]) {
     asm volatile("ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"

@@ -100,7 +100,9 @@ struct Matcher {
                          IW = Cfg::kItemWords;
     MatchSmem sm;
     uint32_t seed, slot_shift, lane, lanemask_lt, one;
-    uint32_t n_slots, ecopy_shift, ecopy;   // entry rows: 2^ecopy_shift copies, this lane reads copy `ecopy`
+    // 32-bit shared addresses of this lane's copy of mask row 0 / entry slot 0 (piece 0), the
+    // shift that turns a slot into a byte offset, and the byte distance between the pieces
+    uint32_t mask_addr, entry_addr, slot_byte_shift, entry_piece_bytes;
     bool two_slot;
     mask_t len_mask;
     uint32_t waiting;   // deferred walks in this warp's queue (warp-uniform)
@@ -146,11 +148,10 @@ struct Matcher {
     // a virtual entry) and whether a longer entry continues it.
     __device__ __forceinline__ bool lookup(const uint32_t (&r)[RW], int L, uint32_t &qid, bool &ext) const {
         uint32_t m[RWP];
-        const uint4 *mrow = reinterpret_cast<const uint4 *>(sm.masks) +
-                            (uint32_t)L * Cfg::kMaskCopies + (lane & (Cfg::kMaskCopies - 1));
+        const uint32_t mrow = mask_addr + (uint32_t)L * (Cfg::kMaskCopies * 16);
 #pragma unroll
         for (int j = 0; j < RWP / 4; ++j) {
-            const uint4 v = mrow[j * (Cfg::kRows * Cfg::kMaskCopies)];
+            const uint4 v = lds_128(mrow + j * (Cfg::kRows * Cfg::kMaskCopies * 16));
             m[4 * j] = v.x; m[4 * j + 1] = v.y; m[4 * j + 2] = v.z; m[4 * j + 3] = v.w;
         }
         uint32_t h = 0;
@@ -162,10 +163,10 @@ struct Matcher {
         const uint32_t tag = hash_finish(h, (uint32_t)L + 1u, seed);
         uint32_t w[EW];
         auto fetch = [&](uint32_t slot) {
-            const uint4 *e = reinterpret_cast<const uint4 *>(sm.entries) + ((slot << ecopy_shift) + ecopy);
+            const uint32_t e = entry_addr + (slot << slot_byte_shift);
 #pragma unroll
             for (int j = 0; j < EW / 4; ++j) {
-                const uint4 v = e[(uint32_t)j * (n_slots << ecopy_shift)];
+                const uint4 v = lds_128(e + (uint32_t)j * entry_piece_bytes);
                 w[4 * j] = v.x; w[4 * j + 1] = v.y; w[4 * j + 2] = v.z; w[4 * j + 3] = v.w;
             }
             uint32_t diff = 0;
@@ -353,9 +354,11 @@ match_count_kernel(const uint8_t *__restrict__ heads, uint64_t n_keys,
     Matcher<NCHUNK> mt;
     mt.sm.masks = smem;
     mt.sm.entries = smem + mask_words;
-    mt.n_slots = n_slots;
-    mt.ecopy_shift = ecopy_shift;
-    mt.ecopy = threadIdx.x & ((1u << ecopy_shift) - 1u);
+    mt.mask_addr = (uint32_t)__cvta_generic_to_shared(smem) + (threadIdx.x & (Cfg::kMaskCopies - 1)) * 16u;
+    mt.entry_addr = (uint32_t)__cvta_generic_to_shared(smem + mask_words) +
+                    (threadIdx.x & ((1u << ecopy_shift) - 1u)) * 16u;
+    mt.slot_byte_shift = ecopy_shift + 4u;
+    mt.entry_piece_bytes = (n_slots << ecopy_shift) * 16u;
     mt.sm.hist = smem + image_words;
     mt.sm.queue = smem + image_words + ((n_prefix + 3u) & ~3u) +
                   (threadIdx.x >> 5) * (queue_items(JOINT) * Cfg::kItemWords);
@@ -374,10 +377,13 @@ match_count_kernel(const uint8_t *__restrict__ heads, uint64_t n_keys,
     // while this step's are examined (two register buffers, the loop is unrolled by two
     // so that they never have to be copied).
     auto load_tile = [&](uint64_t base, uint32_t (&x)[U][XW]) {
+        // a tile that lies inside the snapshot (all but the last one or two of a block) is
+        // loaded without a per-record range test: `base` is the same for the whole block
+        const bool whole = base + (uint64_t)blockDim.x * U <= n_keys;
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             const uint64_t idx = base + (uint64_t)u * blockDim.x + threadIdx.x;
-            if (idx < n_keys) {
+            if (whole || idx < n_keys) {
                 const uint8_t *p = heads + idx * (uint64_t)(16 * NCHUNK);
                 if constexpr (WIDE) {
                     static_assert(!WIDE || NCHUNK % 2 == 0, "256-bit loads need 32-byte records");
