@@ -419,6 +419,22 @@ def run_ours(args):
                'sweep': {'policies': len(SWEEP), 'ms': msS, 'decisions_per_sec': dpsS,
                          'bound': 'integer ALU (41 decisions per 4 loaded bytes)'},
                'pod_ticks_default_policy': int(out1['sums'][0, 0].item())}
+        # the same trace stored as uint16 (BASELINE config 3's "uint16 variant": half the bytes);
+        # the synthetic depths are below 2^16, so the integers are the same
+        if int(trace.max().item()) < 65536:
+            trace16 = trace.to(torch.int16)      # same bits as uint16 below 2^15; the library reads uint16
+            del trace
+            trace = trace16
+            ms16, dps16, out16 = timed([(1, 0, 1)], 10, 3)
+            msS16, dpsS16, outS16 = timed(SWEEP, 2, 1)
+            if int(out16['sums'][0, 0].item()) != rep['pod_ticks_default_policy'] or \
+                    not bool((outS16['sums'] == outS['sums']).all()):
+                raise SystemExit('bench.py: uint16 and int32 traces replay to different integers')
+            gbs16 = Q * T * 2 / (ms16 * 1e-3) / 1e9
+            rep['s1_uint16'] = {'policies': 1, 'ms': ms16, 'decisions_per_sec': dps16,
+                                'roofline': {'bound': 'hbm', 'achieved': gbs16, 'peak': peak, 'unit': 'GB/s',
+                                             'frac': gbs16 / peak, 'algorithmic_bytes_per_launch': Q * T * 2}}
+            rep['sweep_uint16'] = {'policies': len(SWEEP), 'ms': msS16, 'decisions_per_sec': dpsS16}
         del trace
 
     clocks = None

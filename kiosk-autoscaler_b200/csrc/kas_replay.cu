@@ -247,6 +247,145 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
     }
 }
 
+// ---- one policy over a uint16 trace, packed arithmetic ---------------------
+// The uint16 trace halves the bytes of the HBM-bound one-policy replay, but the kernel above
+// then runs out of integer issue slots first (about 11 instructions per decision).  Here a
+// 32-bit word of the trace -- two adjacent resources -- is never taken apart: sm_100's 16-bit
+// pair instructions (VIMNMX.U16x2, VIMNMX3.S16x2, VIADD.16x2) make both decisions at once, and
+// with keys_per_pod == 1 the loaded word already is the pair of quotients.  Same arithmetic as
+// the sweep kernel's packed form (finish_simple3 in kas_decide.cuh); host-side conditions:
+// uint16 trace, no in-progress term, no cur0, no failing patches, one policy with
+// 0 <= min_pods, max_pods <= kPackedMaxPods and 1 <= keys_per_pod <= 2^14.
+constexpr int32_t kPackedMaxPods = 1023;      // x kPackedFlushTicks stays below 2^16
+constexpr uint32_t kPackedFlushTicks = 64;    // 16-bit patch / pod-tick sums are emptied this often
+
+template <bool K1>
+__global__ void __launch_bounds__(kReplayThreads, 4)
+replay_packed16_kernel(const __grid_constant__ ReplayParams P) {
+    constexpr int U = kTickUnroll, W = 4;       // ticks per batch; packed words (pairs of resources) per thread
+    const uint64_t r0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * (2 * W);
+    const bool valid = r0 < P.R;                // R is a multiple of 8 on this path
+    const uint32_t T = P.T;
+    const uint64_t Q = P.Q;
+    const PolDev pol = P.pol[0];
+    const uint32_t mx2 = (uint32_t)pol.mx * 0x00010001u, mn2 = (uint32_t)pol.mn * 0x00010001u;
+    const bool min_positive = pol.mn > 0;       // then every decision is positive and keeps the current pods
+    const bool dense = P.dense != nullptr;
+    uint32_t cur2[W], np2[W], pa2[W];
+    long long pt[2 * W];
+    uint32_t np[2 * W];
+#pragma unroll
+    for (int w = 0; w < W; ++w) { cur2[w] = 0u; np2[w] = 0u; pa2[w] = 0u; }
+#pragma unroll
+    for (int v = 0; v < 2 * W; ++v) { pt[v] = 0; np[v] = 0u; }
+
+    if (valid) {
+        const uint16_t *lrow = static_cast<const uint16_t *>(P.llen) + r0;
+        auto flush = [&]() {
+#pragma unroll
+            for (int w = 0; w < W; ++w) {
+                pt[2 * w] += pa2[w] & 0xFFFFu;  pt[2 * w + 1] += pa2[w] >> 16;
+                np[2 * w] += np2[w] & 0xFFFFu;  np[2 * w + 1] += np2[w] >> 16;
+                pa2[w] = 0u; np2[w] = 0u;
+            }
+        };
+        // one tick: the four words of `row` are this thread's eight resources
+        auto step = [&](uint32_t t, const uint4 &row, auto densetag) {
+            const uint32_t x[W] = {row.x, row.y, row.z, row.w};
+#pragma unroll
+            for (int w = 0; w < W; ++w) {
+                uint32_t q2;
+                if constexpr (K1) {
+                    q2 = x[w];                                               // tally // 1, both halves
+                } else {
+                    const uint32_t qa = quotient_small((x[w] & 0xFFFFu) + 1u, pol);
+                    const uint32_t qb = quotient_small((x[w] >> 16) + 1u, pol);
+                    q2 = __byte_perm(qa, qb, 0x5410);
+                }
+                // keep factor as a mask: all ones when min_pods > 0, else 0xFFFF where q > 0
+                const uint32_t km2 = min_positive ? 0xFFFFFFFFu : __vminu2(q2, 0x00010001u) * 0xFFFFu;
+                const uint32_t c2 = cur2[w];
+                const uint32_t w2 = __vimax3_s16x2(__vminu2(q2, mx2), mn2, c2 & km2);   // autoscaler.py:255-259
+                np2[w] = __vadd2(np2[w], __vminu2(w2 ^ c2, 0x00010001u));            // :227
+                pa2[w] = __vadd2(pa2[w], w2);
+                cur2[w] = w2;
+            }
+            if constexpr (decltype(densetag)::value) {
+                int32_t *o = P.dense + ((uint64_t)P.pol_index[0] * T + t) * P.R + r0;
+                reinterpret_cast<int4 *>(o)[0] = make_int4((int32_t)(cur2[0] & 0xFFFFu), (int32_t)(cur2[0] >> 16),
+                                                           (int32_t)(cur2[1] & 0xFFFFu), (int32_t)(cur2[1] >> 16));
+                reinterpret_cast<int4 *>(o)[1] = make_int4((int32_t)(cur2[2] & 0xFFFFu), (int32_t)(cur2[2] >> 16),
+                                                           (int32_t)(cur2[3] & 0xFFFFu), (int32_t)(cur2[3] >> 16));
+            }
+        };
+        auto load = [&](uint32_t t, uint4 (&rows)[U]) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const uint32_t tt = min(t + (uint32_t)u, T - 1);          // clamped; never used past T
+                const int4 v = ldg_stream_i4(lrow + (uint64_t)tt * Q);
+                rows[u] = make_uint4((uint32_t)v.x, (uint32_t)v.y, (uint32_t)v.z, (uint32_t)v.w);
+            }
+        };
+        auto run = [&](uint32_t t, const uint4 (&rows)[U]) {
+            if (dense) {
+#pragma unroll
+                for (int u = 0; u < U; ++u) step(t + u, rows[u], std::true_type{});
+            } else {
+#pragma unroll
+                for (int u = 0; u < U; ++u) step(t + u, rows[u], std::false_type{});
+            }
+        };
+        // software pipeline: the next U rows are in flight while U rows are consumed
+        uint4 ra[U], rb[U];
+        uint32_t t0 = 0, since_flush = 0;
+        if (T >= 2 * U) {
+            load(0, ra);
+            for (; t0 + 2 * U <= T; t0 += 2 * U) {
+                load(t0 + U, rb);
+                run(t0, ra);
+                load(t0 + 2 * U, ra);
+                run(t0 + U, rb);
+                since_flush += 2 * U;
+                if (since_flush + 2 * U > kPackedFlushTicks) { flush(); since_flush = 0; }
+            }
+        }
+        flush();                                   // the tail below is shorter than 2 * U ticks
+        for (; t0 < T; ++t0) {
+            const int4 v = ldg_stream_i4(lrow + (uint64_t)t0 * Q);
+            const uint4 row = make_uint4((uint32_t)v.x, (uint32_t)v.y, (uint32_t)v.z, (uint32_t)v.w);
+            if (dense) step(t0, row, std::true_type{}); else step(t0, row, std::false_type{});
+        }
+        flush();
+        if (P.totals) {
+#pragma unroll
+            for (int v = 0; v < 2 * W; ++v) {
+                kas_totals o;
+                o.pod_ticks = pt[v];
+                o.n_patches = np[v];
+                o.final_current = (int32_t)((v & 1) ? cur2[v / 2] >> 16 : cur2[v / 2] & 0xFFFFu);
+                P.totals[(r0 + v) * P.S + P.pol_index[0]] = o;
+            }
+        }
+    }
+    if (P.sums) {
+        long long a = 0, b = 0, c = 0;
+        if (valid) {
+#pragma unroll
+            for (int v = 0; v < 2 * W; ++v) {
+                a += pt[v]; b += np[v];
+                c += (long long)((v & 1) ? cur2[v / 2] >> 16 : cur2[v / 2] & 0xFFFFu);
+            }
+        }
+        a = warp_sum_ll(a); b = warp_sum_ll(b); c = warp_sum_ll(c);
+        if ((threadIdx.x & 31) == 0) {
+            unsigned long long *o = P.sums + 3ull * P.pol_index[0];
+            atomicAdd(o + 0, (unsigned long long)a);
+            atomicAdd(o + 1, (unsigned long long)b);
+            atomicAdd(o + 2, (unsigned long long)c);
+        }
+    }
+}
+
 // ---- resources that own several queues (CSR groups) ------------------------
 template <typename E, int SP, int MODE, bool DELAY>
 __global__ void __launch_bounds__(kReplayThreads)
@@ -1042,7 +1181,14 @@ static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream)
             launch_small<E>(P, mode, stream);
         } else if (identity && !a->d_patch_fail && !delayed) {
             if (P.pol_count == 1) {
-                if (vec) launch_identity<E, kVec, 1>(P, mode, stream);
+                const PolDev &pd = P.pol[0];
+                const bool packable = sizeof(E) == 2 && vec && mode != kGeneric && a->inprog_mode == 0 &&
+                                      !a->d_cur0 && pd.mn >= 0 && pd.mx <= kPackedMaxPods && pd.m32 != 0u;
+                if (packable) {
+                    const unsigned grid = (unsigned)((P.R / 8 + kReplayThreads - 1) / kReplayThreads);
+                    if (pd.k1) replay_packed16_kernel<true><<<grid, kReplayThreads, 0, stream>>>(P);
+                    else replay_packed16_kernel<false><<<grid, kReplayThreads, 0, stream>>>(P);
+                } else if (vec) launch_identity<E, kVec, 1>(P, mode, stream);
                 else launch_identity<E, 1, 1>(P, mode, stream);
             } else {
                 if (vec) {

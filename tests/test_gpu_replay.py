@@ -206,6 +206,33 @@ def test_sweep_packed_state(data, dtype, ipmode):
         assert int(want['dense'].max()) == 1023
 
 
+@pytest.mark.parametrize('policy', [(1, 0, 1), (1, 0, 1023), (1, 2, 7), (1, 0, 0), (5, 0, 64), (16384, 0, 3),
+                                    (3, 1, 1), (2, 1023, 1023)])
+@pytest.mark.parametrize('T', [1, 7, 64, 301])
+def test_uint16_single_policy_packed(policy, T):
+    """One policy over a uint16 trace without in-progress term or cur0: the packed kernel
+    (a trace word = two resources, never taken apart).  Counts up to 65535, max_pods = 1023
+    held over the 64-tick emptying of the 16-bit sums, tick counts around the pipeline depth."""
+    import autoscaler
+    from oracle import coracle
+    rng = np.random.default_rng(hash((policy, T)) % (2 ** 32))
+    Q = 8192
+    llen = rng.integers(0, 60, size=(T, Q)).astype(np.uint16)
+    llen[rng.random((T, Q)) < 0.4] = 0
+    llen[rng.random((T, Q)) < 0.01] = 65535
+    llen[:, rng.random(Q) < 0.2] = 40000           # sits at max_pods for the whole trace
+    want = coracle.replay(llen.astype(np.int32), None, None, None, [policy], want_dense=True)
+    got = autoscaler.replay.replay_fleet(llen, [policy], want_dense=True)
+    assert (got.dense == want['dense']).all()
+    assert (got.pod_ticks == want['pod_ticks']).all()
+    assert (got.n_patches == want['n_patches']).all()
+    assert (got.final == want['final']).all()
+    assert (got.sums[0] == [want['pod_ticks'].sum(), want['n_patches'].sum(), want['final'].sum()]).all()
+    got2 = autoscaler.replay.replay_fleet(llen, [policy])
+    assert (got2.pod_ticks == want['pod_ticks']).all() and (got2.n_patches == want['n_patches']).all()
+    assert (got2.final == want['final']).all()
+
+
 def test_synth_trace_twin():
     from autoscaler import engine
     from oracle import coracle
