@@ -423,8 +423,8 @@ replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
 #pragma unroll
             for (int s = 0; s < SP; ++s) sum[s] = 0;
             for (uint64_t q = q0; q < q1; ++q) {
-                const int32_t l = ld_trace<E>(lrow + q);
-                const int32_t ip = P.inprog_mode == 2 ? ld_trace<E>(irow + q)
+                const int32_t l = ld_trace_cached<E>(lrow + q);
+                const int32_t ip = P.inprog_mode == 2 ? ld_trace_cached<E>(irow + q)
                                                       : (P.inprog_mode == 1 ? __ldg(iq + q) : 0);
 #pragma unroll
                 for (int s = 0; s < SP; ++s)
@@ -1025,6 +1025,172 @@ synth_trace_kernel(uint64_t seed, uint32_t T, uint64_t q_first, uint64_t n_q, in
     }
 }
 
+// ---- resources that own several queues, trace staged in shared memory ------
+// replay_grouped_kernel above reads the trace element by element: a thread's loads of one
+// tick depend on nothing, but nothing makes them early either, and neighbouring threads
+// touch the same sectors again and again (measured 0.67-0.86 TB/s).  Here the block -- 128
+// consecutive resources, whose queues are one contiguous run of the queue axis -- copies that
+// run for a tile of ticks into shared memory with 16-byte cp.async pieces, two tiles in
+// flight, and the threads then replay their resource out of shared memory.  The run is
+// widened to 16-byte boundaries, which needs 16-byte aligned rows (host-checked).  A block
+// whose run does not fit a tile even for one tick takes the direct loads.
+constexpr int kGroupedTileBytes = 24 * 1024;     // per stage and array; 4 blocks per SM
+constexpr int kGroupedStages = 2;
+constexpr uint32_t kGroupedMaxTileTicks = 32;
+
+template <typename E, int SP, int MODE, bool TICKIP>
+__global__ void __launch_bounds__(kReplayThreads)
+replay_grouped_tiled_kernel(const __grid_constant__ ReplayParams P) {
+    constexpr uint32_t kEPP = 16 / sizeof(E);
+    constexpr uint32_t kTileVec = kGroupedTileBytes / 16;     // int4 per stage and array
+    extern __shared__ int4 gsm[];                              // [stages][TICKIP ? 2 : 1][kTileVec]
+    const uint32_t ny = (P.pol_count + SP - 1) / SP;
+    const uint32_t pbase = (blockIdx.x % ny) * SP;
+    const uint64_t rb = (uint64_t)(blockIdx.x / ny) * blockDim.x;      // first resource of the block
+    const uint64_t r = rb + threadIdx.x;
+    const bool valid = r < P.R;
+    const uint32_t T = P.T;
+    const uint64_t Q = P.Q;
+    // the block's run of the queue axis, widened to whole 16-byte pieces
+    const uint64_t r_end = min(rb + (uint64_t)blockDim.x, P.R);
+    const uint64_t qa = P.group_off[rb], qb = P.group_off[r_end];
+    const uint64_t a0 = qa & ~(uint64_t)(kEPP - 1);
+    const uint64_t a1 = (qb + kEPP - 1) & ~(uint64_t)(kEPP - 1);       // <= Q: Q is a multiple of kEPP
+    const uint64_t row_vec64 = (a1 - a0) / kEPP;                        // int4 per tick
+    const uint32_t tile_ticks = row_vec64 == 0 ? kGroupedMaxTileTicks
+                                : (uint32_t)min((uint64_t)kGroupedMaxTileTicks, (uint64_t)kTileVec / row_vec64);
+    const bool tiled = tile_ticks > 0;                                  // uniform over the block
+    const uint32_t row_vec = (uint32_t)row_vec64;
+    int32_t cur[SP];
+    long long pt[SP];
+    uint32_t np[SP];
+    const int32_t c0 = (valid && P.cur0) ? P.cur0[r] : 0;
+#pragma unroll
+    for (int s = 0; s < SP; ++s) { cur[s] = c0; pt[s] = 0; np[s] = 0u; }
+    const uint64_t q0 = valid ? P.group_off[r] : 0, q1 = valid ? P.group_off[r + 1] : 0;
+    const int32_t *iq = static_cast<const int32_t *>(P.inprog);          // per-queue term
+    // this thread's policies in registers; slots past the end repeat the last one, unwritten
+    PolDev pol[SP];
+    bool live[SP];
+#pragma unroll
+    for (int s = 0; s < SP; ++s) {
+        live[s] = pbase + s < P.pol_count;
+        pol[s] = P.pol[live[s] ? pbase + s : P.pol_count - 1];
+    }
+    const uint32_t n_own = (uint32_t)min(q1 - q0, (uint64_t)0xFFFFFFFFu);   // queues of this resource
+    const bool huge = q1 - q0 > 0xFFFFFFFFull;                              // (never tiled then)
+
+    // one tick of this thread's resource; LOAD(q) -> (llen, inprog) of queue q at this tick
+    auto tick = [&](uint32_t t, auto load) {
+        const bool failed = P.patch_fail && P.patch_fail[(uint64_t)t * P.R + r];
+        long long sum[SP];
+#pragma unroll
+        for (int s = 0; s < SP; ++s) sum[s] = 0;
+        auto one_queue = [&](uint64_t q) {
+            int32_t l, ip;
+            load(q, l, ip);
+#pragma unroll
+            for (int s = 0; s < SP; ++s) sum[s] += decide<MODE>(l, ip, pol[s], cur[s]);   // autoscaler.py:255-257
+        };
+        if (!huge) {
+            for (uint32_t j = 0; j < n_own; ++j) one_queue(q0 + j);
+        } else {
+            for (uint64_t q = q0; q < q1; ++q) one_queue(q);
+        }
+#pragma unroll
+        for (int s = 0; s < SP; ++s) {
+            if (live[s]) {
+                const PolDev &p = pol[s];
+                const int32_t want = clip64(sum[s], p.mn, p.mx, cur[s]);          // :259
+                if (want != cur[s]) {                                             // :227
+                    np[s] += 1;                                                   // the patch call is made
+                    if (!failed) cur[s] = want;                                   // raised and swallowed: :267-273
+                }
+                pt[s] += cur[s];
+                if (P.dense) P.dense[((uint64_t)P.pol_index[pbase + s] * T + t) * P.R + r] = cur[s];
+            }
+        }
+    };
+
+    if (tiled) {
+        const uint32_t n_tiles = (T + tile_ticks - 1) / tile_ticks;
+        auto stage = [&](uint32_t k) {
+            if (k < n_tiles) {
+                const uint32_t t0 = k * tile_ticks;
+                const uint32_t nt = min(tile_ticks, T - t0);
+                int4 *dl = gsm + (k % kGroupedStages) * (TICKIP ? 2 : 1) * kTileVec;
+                int4 *di = dl + kTileVec;
+                for (uint32_t e = threadIdx.x; e < nt * row_vec; e += blockDim.x) {
+                    const uint32_t t = e / row_vec, c = e - t * row_vec;
+                    const uint64_t g = (uint64_t)(t0 + t) * Q + a0 + (uint64_t)kEPP * c;
+                    cp_async_16(dl + e, static_cast<const E *>(P.llen) + g);
+                    if (TICKIP) cp_async_16(di + e, static_cast<const E *>(P.inprog) + g);
+                }
+            }
+            cp_async_commit();
+        };
+        stage(0);
+        for (uint32_t k = 0; k < n_tiles; ++k) {
+            stage(k + 1);                  // its buffer was released by the barrier that ended tile k-1
+            cp_async_wait<1>();            // this thread's pieces of tile k have landed
+            __syncthreads();               // ... and everybody else's
+            if (valid) {
+                const uint32_t t0 = k * tile_ticks;
+                const uint32_t nt = min(tile_ticks, T - t0);
+                const E *tl = reinterpret_cast<const E *>(gsm + (k % kGroupedStages) * (TICKIP ? 2 : 1) * kTileVec);
+                const E *ti = tl + (size_t)kTileVec * kEPP;
+                const uint32_t row_elems = row_vec * kEPP;
+                for (uint32_t t = 0; t < nt; ++t) {
+                    const E *lrow = tl + (size_t)t * row_elems;
+                    const E *irow = ti + (size_t)t * row_elems;
+                    tick(t0 + t, [&](uint64_t q, int32_t &l, int32_t &ip) {
+                        const uint32_t j = (uint32_t)(q - a0);          // place inside the staged run
+                        l = (int32_t)lrow[j];
+                        ip = TICKIP ? (int32_t)irow[j] : (P.inprog_mode == 1 ? __ldg(iq + q) : 0);
+                    });
+                }
+            }
+            __syncthreads();               // everybody is done with tile k
+        }
+        cp_async_wait<0>();
+    } else if (valid) {
+        for (uint32_t t = 0; t < T; ++t) {
+            const E *lrow = static_cast<const E *>(P.llen) + (uint64_t)t * Q;
+            const E *irow = static_cast<const E *>(P.inprog) + (uint64_t)t * Q;
+            tick(t, [&](uint64_t q, int32_t &l, int32_t &ip) {
+                l = ld_trace_cached<E>(lrow + q);
+                ip = TICKIP ? ld_trace_cached<E>(irow + q) : (P.inprog_mode == 1 ? __ldg(iq + q) : 0);
+            });
+        }
+    }
+    if (valid && P.totals) {
+#pragma unroll
+        for (int s = 0; s < SP; ++s)
+            if (live[s]) {
+                kas_totals o;
+                o.pod_ticks = pt[s];
+                o.n_patches = np[s];
+                o.final_current = cur[s];
+                P.totals[r * P.S + P.pol_index[pbase + s]] = o;
+            }
+    }
+    if (P.sums) {
+#pragma unroll
+        for (int s = 0; s < SP; ++s) {
+            if (live[s]) {
+                long long a = valid ? pt[s] : 0, b = valid ? (long long)np[s] : 0, c = valid ? (long long)cur[s] : 0;
+                a = warp_sum_ll(a); b = warp_sum_ll(b); c = warp_sum_ll(c);
+                if ((threadIdx.x & 31) == 0) {
+                    unsigned long long *o = P.sums + 3ull * P.pol_index[pbase + s];
+                    atomicAdd(o + 0, (unsigned long long)a);
+                    atomicAdd(o + 1, (unsigned long long)b);
+                    atomicAdd(o + 2, (unsigned long long)c);
+                }
+            }
+        }
+    }
+}
+
 template <typename E, int VEC, int SP>
 static void launch_identity(const ReplayParams &P, int mode, cudaStream_t stream) {
     const uint64_t threads = (P.R + VEC - 1) / VEC;
@@ -1090,17 +1256,40 @@ static void launch_small(const ReplayParams &P, int mode, cudaStream_t stream) {
 }
 
 template <typename E, int SP>
-static void launch_grouped(const ReplayParams &P, int mode, cudaStream_t stream) {
+static int launch_grouped(const ReplayParams &P, int mode, cudaStream_t stream) {
     const uint64_t nx = (P.R + kReplayThreads - 1) / kReplayThreads;
     const uint32_t ny = (P.pol_count + SP - 1) / SP;
     const unsigned grid = (unsigned)(nx * ny);
     if (P.startup_delay) {
         if (mode != kGeneric) replay_grouped_kernel<E, SP, kSimple, true><<<grid, kReplayThreads, 0, stream>>>(P);
         else replay_grouped_kernel<E, SP, kGeneric, true><<<grid, kReplayThreads, 0, stream>>>(P);
-    } else {
-        if (mode != kGeneric) replay_grouped_kernel<E, SP, kSimple, false><<<grid, kReplayThreads, 0, stream>>>(P);
-        else replay_grouped_kernel<E, SP, kGeneric, false><<<grid, kReplayThreads, 0, stream>>>(P);
+        return KAS_OK;
     }
+    // rows that start on 16-byte boundaries and real groups: the shared-memory tiled kernel
+    constexpr uint64_t kEPP = 16 / sizeof(E);
+    const bool tickip = P.inprog_mode == 2;
+    const bool tileable = P.group_off != nullptr && P.Q % kEPP == 0 && aligned(P.llen, 16) &&
+                          (!tickip || aligned(P.inprog, 16));
+    if (tileable) {
+        const size_t smem = (size_t)kGroupedStages * (tickip ? 2 : 1) * kGroupedTileBytes;
+#define KAS_LAUNCH_GT(MD, TI)                                                                      \
+    do {                                                                                           \
+        auto kern = replay_grouped_tiled_kernel<E, SP, MD, TI>;                                    \
+        KAS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
+                                          (int)smem));                                             \
+        kern<<<grid, kReplayThreads, smem, stream>>>(P);                                           \
+    } while (0)
+        if (mode != kGeneric) {
+            if (tickip) KAS_LAUNCH_GT(kSimple, true); else KAS_LAUNCH_GT(kSimple, false);
+        } else {
+            if (tickip) KAS_LAUNCH_GT(kGeneric, true); else KAS_LAUNCH_GT(kGeneric, false);
+        }
+#undef KAS_LAUNCH_GT
+        return KAS_OK;
+    }
+    if (mode != kGeneric) replay_grouped_kernel<E, SP, kSimple, false><<<grid, kReplayThreads, 0, stream>>>(P);
+    else replay_grouped_kernel<E, SP, kGeneric, false><<<grid, kReplayThreads, 0, stream>>>(P);
+    return KAS_OK;
 }
 
 }  // namespace kas
@@ -1199,8 +1388,9 @@ static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream)
                 }
             }
         } else {
-            if (P.pol_count == 1) launch_grouped<E, 1>(P, mode, stream);
-            else launch_grouped<E, 4>(P, mode, stream);
+            const int st = P.pol_count == 1 ? launch_grouped<E, 1>(P, mode, stream)
+                                            : launch_grouped<E, 4>(P, mode, stream);
+            if (st != KAS_OK) return st;
         }
         KAS_CUDA_TRY(cudaGetLastError());
     }
