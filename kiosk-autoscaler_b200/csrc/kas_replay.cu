@@ -1034,7 +1034,10 @@ synth_trace_kernel(uint64_t seed, uint32_t T, uint64_t q_first, uint64_t n_q, in
 // flight, and the threads then replay their resource out of shared memory.  The run is
 // widened to 16-byte boundaries, which needs 16-byte aligned rows (host-checked).  A block
 // whose run does not fit a tile even for one tick takes the direct loads.
-constexpr int kGroupedTileBytes = 24 * 1024;     // per stage and array; 4 blocks per SM
+#ifndef KAS_GROUPED_TILE_KB
+#define KAS_GROUPED_TILE_KB 12   /* 8 blocks per SM: this kernel lives on latency hiding (24 KB: 8.1 ms, 12 KB: 6.7 ms) */
+#endif
+constexpr int kGroupedTileBytes = KAS_GROUPED_TILE_KB * 1024;     // per stage and array
 constexpr int kGroupedStages = 2;
 constexpr uint32_t kGroupedMaxTileTicks = 32;
 
