@@ -1089,16 +1089,38 @@ replay_grouped_tiled_kernel(const __grid_constant__ ReplayParams P) {
         long long sum[SP];
 #pragma unroll
         for (int s = 0; s < SP; ++s) sum[s] = 0;
-        auto one_queue = [&](uint64_t q) {
+        // Simple arithmetic first, with no test per queue: the signs of everything read are
+        // collected, and a tick that saw a negative count is summed again the exact way.
+        int32_t any = 0;
+        auto one_queue = [&](uint64_t q, auto fasttag) {
             int32_t l, ip;
             load(q, l, ip);
+            if constexpr (decltype(fasttag)::value) {
+                any |= l | ip;
 #pragma unroll
-            for (int s = 0; s < SP; ++s) sum[s] += decide<MODE>(l, ip, pol[s], cur[s]);   // autoscaler.py:255-257
+                for (int s = 0; s < SP; ++s)
+                    sum[s] += decide_simple<false>((uint32_t)l + (uint32_t)ip, pol[s], cur[s]);   // autoscaler.py:255-257
+            } else {
+#pragma unroll
+                for (int s = 0; s < SP; ++s) sum[s] += decide_exact(l, ip, pol[s], cur[s]);
+            }
         };
-        if (!huge) {
-            for (uint32_t j = 0; j < n_own; ++j) one_queue(q0 + j);
+        auto all_queues = [&](auto fasttag) {
+            if (!huge) {
+                for (uint32_t j = 0; j < n_own; ++j) one_queue(q0 + j, fasttag);
+            } else {
+                for (uint64_t q = q0; q < q1; ++q) one_queue(q, fasttag);
+            }
+        };
+        if constexpr (MODE != kGeneric) {
+            all_queues(std::true_type{});
+            if (any < 0) {
+#pragma unroll
+                for (int s = 0; s < SP; ++s) sum[s] = 0;
+                all_queues(std::false_type{});
+            }
         } else {
-            for (uint64_t q = q0; q < q1; ++q) one_queue(q);
+            all_queues(std::false_type{});
         }
 #pragma unroll
         for (int s = 0; s < SP; ++s) {
