@@ -162,3 +162,30 @@ def test_heads_equivalence_and_c_vs_numpy_replay():
     assert (c['dense'] == d['dense']).all() and (c['pod_ticks'] == d['pod_ticks']).all()
     assert (c['n_patches'] == d['n_patches']).all()
     assert b['pod_ticks'].shape == a['pod_ticks'].shape
+
+
+def test_python_and_c_oracle_agree_on_random_replays():
+    """The two restatements (oracle.py line by line, kas_oracle.c for big sizes) against each
+    other on random single resources: any keys_per_pod sign, min > max, negative counts,
+    failing patches and the start-up delay of the `only_running` reading."""
+    import random
+    rnd = random.Random(7)
+    for case in range(300):
+        nq = rnd.choice([1, 1, 2, 5])
+        T = rnd.randint(1, 60)
+        kpp = rnd.choice([1, 1, 2, 3, 7, 50, -1, -3])
+        mn = rnd.choice([0, 0, 1, 3, -2])
+        mx = rnd.choice([0, 1, 4, 16, 2, -1])
+        cur0 = rnd.choice([0, 0, 1, 5, 40])
+        delay = rnd.choice([0, 0, 1, 2, 5, 9])
+        lo = -5 if rnd.random() < 0.2 else 0
+        depths = [[rnd.choice([0, 0, 0, rnd.randint(lo, 40)]) for _ in range(nq)] for _ in range(T)]
+        fails = [rnd.random() < 0.2 for _ in range(T)] if rnd.random() < 0.4 else None
+        after, patches = oracle.replay_resource(depths, None, kpp, mn, mx, cur0, fails, startup_delay=delay)
+        res = coracle.replay(np.array(depths, dtype=np.int32), None, np.array([0, nq], dtype=np.uint64),
+                             [cur0], [(kpp, mn, mx)], want_dense=True,
+                             patch_fail=None if fails is None else np.array(fails).reshape(-1, 1),
+                             startup_delay=delay)
+        assert res['dense'][0, :, 0].tolist() == after, case
+        assert res['n_patches'][0, 0] == len(patches), case
+        assert res['pod_ticks'][0, 0] == sum(after), case
