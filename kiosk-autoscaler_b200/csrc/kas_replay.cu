@@ -259,8 +259,11 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
 constexpr int32_t kPackedMaxPods = 1023;      // x kPackedFlushTicks stays below 2^16
 constexpr uint32_t kPackedFlushTicks = 64;    // 16-bit patch / pod-tick sums are emptied this often
 
+#ifndef KAS_PACKED16_MINB
+#define KAS_PACKED16_MINB 8   /* 64 registers (a few spilled): latency hiding beats register comfort here (4: 1.322 ms, 8: 1.279 ms per 8 GB) */
+#endif
 template <bool K1>
-__global__ void __launch_bounds__(kReplayThreads, 4)
+__global__ void __launch_bounds__(kReplayThreads, KAS_PACKED16_MINB)
 replay_packed16_kernel(const __grid_constant__ ReplayParams P) {
     constexpr int U = kTickUnroll, W = 4;       // ticks per batch; packed words (pairs of resources) per thread
     const uint64_t r0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) * (2 * W);
