@@ -75,7 +75,7 @@ __device__ __forceinline__ long long warp_sum_ll(long long v) {
 #define KAS_REPLAY_SWEEP_SP 2     // policies per thread under a sweep
 #endif
 #ifndef KAS_REPLAY_MINB_S1
-#define KAS_REPLAY_MINB_S1 6      // resident blocks per SM (register budget), one policy per thread
+#define KAS_REPLAY_MINB_S1 7      // resident blocks per SM (register budget), one policy per thread (6: 2.605 ms, 7: 2.450 ms, 8: 3.344 ms per 16 GB)
 #endif
 #ifndef KAS_REPLAY_MINB_SWEEP
 #define KAS_REPLAY_MINB_SWEEP 4   // the same with several policies per thread
