@@ -345,3 +345,18 @@ def test_short_quotient_magic_numbers_are_exact():
     k = 1 << 14
     m = ((1 << 32) + k - 1) // k - 1
     assert (((1 << 18) + 1) * m) >> 32 != (1 << 18) // k
+
+
+def test_startup_delay_limits_agree():
+    """include/kas.h, the ctypes layer and the argument checks name the same limit."""
+    from autoscaler import engine
+    hdr = open(os.path.join(ROOT, 'include', 'kas.h')).read()
+    m = re.search(r'#define\s+KAS_MAX_STARTUP_DELAY\s+(\d+)u', hdr)
+    assert m and int(m.group(1)) == engine.MAX_STARTUP_DELAY
+    assert 'startup_delay' in dict(engine.ReplayArgs._fields_)
+    assert engine.ReplayArgs._fields_[-1][0] == 'startup_delay'       # appended, older callers zero it
+    with pytest.raises(ValueError):
+        engine._check_delay(engine.MAX_STARTUP_DELAY + 1)
+    with pytest.raises(ValueError):
+        engine._check_delay(-1)
+    assert engine._check_delay(0) == 0
