@@ -9,6 +9,17 @@
 // dependent (cur[t+1] = desired[t]); resources and policies are independent,
 // so a thread owns VEC adjacent resources x SP policies and marches down the
 // tick-major trace, whose rows a warp reads as one contiguous 128/512-byte run.
+//
+// Kernels, chosen by replay_typed() at the bottom of this file:
+//   replay_identity_kernel        single-queue resources, one policy (or a few, unvectorised)
+//   replay_packed16_kernel        the same for a uint16 trace and a realistic policy: two
+//                                 resources per register, 16-bit pair instructions
+//   replay_sweep_kernel           single-queue resources under a policy sweep: trace tiles in
+//                                 shared memory (TMA bulk copies), state 64 / 32 / 16 bits wide
+//   replay_grouped_tiled_kernel   multi-queue resources, the block's run of queues staged in
+//   replay_grouped_kernel         shared memory; the plain one also models the start-up delay
+//   replay_small_kernel           few resources: a warp per resource, lanes are policies
+//   decide_kernel, synth_trace_kernel
 #include "kas_common.cuh"
 #include "kas_decide.cuh"
 
