@@ -360,3 +360,24 @@ def test_startup_delay_limits_agree():
     with pytest.raises(ValueError):
         engine._check_delay(-1)
     assert engine._check_delay(0) == 0
+
+
+def test_keep_factor_form_of_the_decision_is_the_reference_clip():
+    """csrc/kas_decide.cuh, finish_simple3: for keys_per_pod >= 1, min <= max, max >= 0 and a
+    non-negative tally,  max(min(q, max), min, cur * keep)  with
+    keep = min(q + (min > 0), max > 0)  is get_desired_pods (autoscaler.py:197-219) -- the form
+    the sweep kernels compute.  Exhaustive over a small box, any current pods (also negative)."""
+    from oracle import oracle
+    for kpp in (1, 2, 3):
+        for tally in range(0, 31):
+            q = tally // kpp
+            for mx in range(0, 7):
+                for mn in range(-2, mx + 1):
+                    keep = min(q + (1 if mn > 0 else 0), 1 if mx > 0 else 0)
+                    for cur in range(-2, 10):
+                        want = oracle.get_desired_pods(tally, kpp, mn, mx, cur)
+                        got = max(min(q, mx), mn, cur * keep)
+                        if mx == 0 and cur > 0 and q > 0:
+                            # the one place the three-term form needs keep = 0: max_pods == 0
+                            assert keep == 0
+                        assert got == want, (kpp, tally, mn, mx, cur)
