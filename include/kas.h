@@ -14,8 +14,11 @@
  *   - plain C types, no torch / C++ types; return 0 (KAS_OK) or a negative
  *     kas_status; nothing throws across the boundary.
  *   - the CALLER owns every device buffer ("d_" prefix) and every host buffer;
- *     the library allocates no device memory and keeps no global mutable state
- *     besides a per-thread copy of the last CUDA error string.
+ *     the library allocates no device memory.  Its only global mutable state is
+ *     a per-thread copy of the last CUDA error string, a per-thread cache of the
+ *     current device's SM count, and -- for kas_patch_event_offsets_static
+ *     alone -- one fixed 64 KB device array per GPU plus the per-device cache of
+ *     its address (see that entry point for the sharing rules).
  *   - all device work is enqueued on the given stream and is asynchronous with
  *     respect to the host; `stream` is a cudaStream_t passed as void*.
  *   - integer results are bit-exact with the reference's Python arithmetic
@@ -206,7 +209,15 @@ typedef struct kas_replay_args {
     uint32_t n_ticks;           /* T                                               */
     uint64_t n_queues;          /* Q                                               */
     uint64_t n_resources;       /* R (== Q when d_group_off is NULL)               */
-    const uint64_t *d_group_off;/* [R+1] CSR offsets into the queue axis, or NULL  */
+    const uint64_t *d_group_off;/* [R+1] CSR offsets into the queue axis, or NULL.
+                                   Expected non-decreasing with group_off[R] <= Q
+                                   (a resource's queues are one contiguous run).
+                                   Offsets that go back or overlap are not an error
+                                   as long as every one is <= Q: a range that goes
+                                   back is empty, overlapping ranges are each summed;
+                                   the kernels that stage runs in shared memory check
+                                   this per block and read such blocks element by
+                                   element.  An offset beyond Q reads out of bounds. */
     const int32_t *d_cur0;      /* [R] replicas before tick 0, or NULL for zeros   */
     const kas_policy *policies; /* HOST pointer, [S]                               */
     uint32_t n_policies;        /* S                                               */

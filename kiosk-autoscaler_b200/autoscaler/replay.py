@@ -37,6 +37,7 @@ class ReplayResult(object):
         self.sums = sums
         self.dense = dense
         self._cur0 = None
+        self._bodies_from_dense = True
 
     def pod_hours(self, interval_seconds=5):
         """Box-wide pod-hours per policy; INTERVAL as in scale.py:84."""
@@ -44,7 +45,15 @@ class ReplayResult(object):
 
     def patch_bodies(self, resource_type='deployment', resource=0, policy=0):
         """The bodies scale_resource would have sent (autoscaler.py:232,236),
-        reconstructed from the dense trajectory of one resource."""
+        reconstructed from the dense trajectory of one resource.  A replay with
+        failing patch calls or a start-up delay makes calls that leave no trace in the
+        trajectory (a failed call; a repeated patch of the value already in the spec):
+        take those from ``patch_events`` (PatchLog.bodies)."""
+        if not self._bodies_from_dense:
+            raise ValueError('this replay ran with patch_fail / startup_delay: its patch calls '
+                             'cannot be read off the trajectory; use autoscaler.replay.patch_events')
+        if self.dense is None:
+            raise ValueError('patch_bodies needs the dense trajectory (want_dense=True)')
         field = RESOURCE_FIELD[resource_type]
         out = []
         prev = int(self._cur0[resource])
@@ -171,6 +180,7 @@ def replay_fleet(llen, policies, inprog=None, group_off=None, cur0=None, want_to
                        sums=out['sums'].cpu().numpy(),
                        dense=out['dense'].cpu().numpy() if want_dense else None, n_ticks=T)
     res._cur0 = np.zeros(R, dtype=np.int64) if cur0 is None else np.asarray(cur0, dtype=np.int64)
+    res._bodies_from_dense = patch_fail is None and _delay_for(resource_type, startup_delay) == 0
     return res
 
 

@@ -1076,7 +1076,6 @@ replay_grouped_tiled_kernel(const __grid_constant__ ReplayParams P) {
     const uint64_t row_vec64 = (a1 - a0) / kEPP;                        // int4 per tick
     const uint32_t tile_ticks = row_vec64 == 0 ? kGroupedMaxTileTicks
                                 : (uint32_t)min((uint64_t)kGroupedMaxTileTicks, (uint64_t)kTileVec / row_vec64);
-    const bool tiled = tile_ticks > 0;                                  // uniform over the block
     const uint32_t row_vec = (uint32_t)row_vec64;
     int32_t cur[SP];
     long long pt[SP];
@@ -1085,6 +1084,10 @@ replay_grouped_tiled_kernel(const __grid_constant__ ReplayParams P) {
 #pragma unroll
     for (int s = 0; s < SP; ++s) { cur[s] = c0; pt[s] = 0; np[s] = 0u; }
     const uint64_t q0 = valid ? P.group_off[r] : 0, q1 = valid ? P.group_off[r + 1] : 0;
+    // The staged run covers this block's queues only if the offsets do not go back or leave
+    // [0, Q]; a block that sees such offsets reads element by element, like the plain kernel.
+    const bool stray = !(qa <= qb && qb <= Q) || (valid && !(qa <= q0 && q0 <= q1 && q1 <= qb));
+    const bool tiled = !__syncthreads_or(stray ? 1 : 0) && tile_ticks > 0;   // uniform over the block
     const int32_t *iq = static_cast<const int32_t *>(P.inprog);          // per-queue term
     // this thread's policies in registers; slots past the end repeat the last one, unwritten
     PolDev pol[SP];
@@ -1230,6 +1233,304 @@ replay_grouped_tiled_kernel(const __grid_constant__ ReplayParams P) {
     }
 }
 
+// ---- multi-queue resources, the lean form ------------------------------------
+// The tiled kernel above spends about 40 instructions per (queue, tick) with 20 of 32 lanes
+// busy: neighbouring threads own groups of different sizes, so a warp runs as long as its
+// largest group, and everything is carried in 64 bits.  This kernel serves the common case --
+// realistic policies (1 <= keys_per_pod <= 2^14, 0 <= max_pods < 2^20, min <= max), no cur0, no
+// failing patches, no dense output -- with
+//   * threads SORTED by group size inside the block (a counting sort in shared memory), so the
+//     lanes of a warp own groups of one size and the per-queue loop is unrolled for it; the
+//     warps of a block are rotated by a hash of the block index, because the heavy warps of
+//     all blocks would otherwise meet on one scheduler;
+//   * the block's run of the queue axis staged tile by tile with one TMA bulk copy per tick row
+//     (three stages on mbarriers): no thread spends an instruction on moving the trace;
+//   * 32-bit arithmetic: the quotient is one multiply-high (quotient_small), clamp and
+//     hysteresis are min / keep factor / three-input maximum as in the sweep kernel
+//     (kas_decide.cuh), for the per-queue decisions (autoscaler.py:255-257) and for the clip of
+//     their sum (:259) alike.  A tick that holds a count outside [0, 2^16) is replayed by the
+//     exact 64-bit code.
+// Offsets that are not non-decreasing inside [0, Q], a group of 2048 queues or more, a run too
+// wide for a tile: that block reads the trace element by element with the exact arithmetic.
+#ifndef KAS_GS_STAGE_KB
+#define KAS_GS_STAGE_KB 12
+#endif
+constexpr int kGsThreads = 128;
+constexpr int kGsStages = 3;
+constexpr uint32_t kGsStageBytes = KAS_GS_STAGE_KB * 1024;   // per stage and array
+constexpr uint32_t kGsMaxTileTicks = 32;
+constexpr uint32_t kGsMaxOwn = 2048;          // queues of one resource: x kGsMaxPods stays below 2^31
+constexpr int32_t kGsMaxPods = 1 << 20;
+
+template <typename E, int SP, int IPMODE, bool K1>
+__global__ void __launch_bounds__(kGsThreads)
+replay_grouped_sorted_kernel(const __grid_constant__ ReplayParams P) {
+    constexpr uint32_t kEPP = 16 / sizeof(E);
+    constexpr uint32_t kStageVec = kGsStageBytes / 16;
+    constexpr uint32_t kArrays = IPMODE == 2 ? 2u : 1u;
+    constexpr bool kCheck = sizeof(E) == 4;     // a uint16 element is neither negative nor >= 2^16
+    extern __shared__ int4 gsm[];               // [stages][kArrays][kStageVec]; IPMODE 1: + int32 [kStageVec * kEPP]
+    __shared__ uint64_t bars[kGsStages];
+    __shared__ uint32_t s_cnt[33];
+    __shared__ uint16_t s_perm[kGsThreads];
+
+    const uint32_t tid = threadIdx.x;
+    const uint32_t ny = (P.pol_count + SP - 1) / SP;
+    const uint32_t pbase = (blockIdx.x % ny) * SP;
+    const uint32_t bx = blockIdx.x / ny;
+    const uint64_t rb = (uint64_t)bx * kGsThreads;                       // first resource of the block
+    const uint32_t nres = (uint32_t)min((uint64_t)kGsThreads, P.R - rb);
+    const uint32_t T = P.T;
+    const uint64_t Q = P.Q;
+
+    // the block's run of the queue axis, widened to whole 16-byte pieces
+    const uint64_t qa = P.group_off[rb], qb = P.group_off[rb + nres];
+    bool bad = !(qa <= qb && qb <= Q);
+    const uint64_t a0 = qa & ~(uint64_t)(kEPP - 1);
+    const uint64_t a1 = (qb + kEPP - 1) & ~(uint64_t)(kEPP - 1);          // <= Q: Q is a multiple of kEPP
+    const uint64_t row_vec64 = bad ? 0 : (a1 - a0) / kEPP;                // int4 per tick
+    if (row_vec64 > kStageVec) bad = true;
+
+    // counting sort of the block's resources by group size
+    uint32_t key = 0, pos = 0;
+    if (tid < nres) {
+        const uint64_t g0 = P.group_off[rb + tid], g1 = P.group_off[rb + tid + 1];
+        if (!(g0 <= g1 && qa <= g0 && g1 <= qb) || g1 - g0 >= kGsMaxOwn) bad = true;
+        else key = (uint32_t)min(g1 - g0, (uint64_t)32);
+    }
+    if (tid < 33) s_cnt[tid] = 0u;
+    s_perm[tid] = 0xFFFFu;
+    if (tid == 0) {
+#pragma unroll
+        for (int i = 0; i < kGsStages; ++i) mbar_init(&bars[i], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (tid < nres) pos = atomicAdd(&s_cnt[key], 1u);
+    __syncthreads();
+    if (tid < 32) {
+        const uint32_t c = s_cnt[tid];
+        uint32_t incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (tid >= (uint32_t)o) incl += v;
+        }
+        const uint32_t tot = __shfl_sync(0xFFFFFFFFu, incl, 31);
+        s_cnt[tid] = incl - c;            // first place of size class `tid`
+        if (tid == 0) s_cnt[32] = tot;    // ... and of the class "32 queues or more"
+    }
+    __syncthreads();
+    if (tid < nres) {
+        const uint32_t p = s_cnt[key] + pos;
+        const uint32_t rot = (bx * 2654435761u) >> 30;                   // 0..3
+        s_perm[((((p >> 5) + rot) & 3u) << 5) | (p & 31u)] = (uint16_t)tid;
+    }
+    // the per-queue in-progress counts of the run, once (IPMODE 1)
+    int32_t *s_ipq = reinterpret_cast<int32_t *>(gsm + kGsStages * kArrays * kStageVec);
+    if constexpr (IPMODE == 1) {
+        if (row_vec64 <= kStageVec) {
+            const uint32_t row_elems0 = (uint32_t)row_vec64 * kEPP;
+            const int32_t *iq = static_cast<const int32_t *>(P.inprog) + a0;
+            for (uint32_t i = tid; i < row_elems0; i += kGsThreads) {
+                const int32_t v = __ldg(iq + i);
+                s_ipq[i] = v;
+                if ((uint32_t)v >= kSmallTallyTerm && a0 + i >= qa && a0 + i < qb) bad = true;
+            }
+        }
+    }
+    const bool tiled = !__syncthreads_or(bad ? 1 : 0);                   // uniform over the block
+
+    const uint32_t mine = s_perm[tid];
+    const bool valid = tiled ? mine != 0xFFFFu : tid < nres;
+    const uint64_t r = rb + (tiled ? (valid ? mine : 0u) : tid);
+    const uint64_t q0 = valid ? P.group_off[r] : 0, q1 = valid ? P.group_off[r + 1] : 0;
+
+    PolDev pol[SP];
+    bool live[SP];
+    KeepTerm keep[SP];
+#pragma unroll
+    for (int s = 0; s < SP; ++s) {
+        live[s] = pbase + s < P.pol_count;
+        pol[s] = P.pol[live[s] ? pbase + s : P.pol_count - 1];
+        keep[s] = keep_term(pol[s]);
+    }
+    int32_t cur[SP];
+    long long pt[SP];
+    uint32_t np[SP];
+#pragma unroll
+    for (int s = 0; s < SP; ++s) { cur[s] = 0; pt[s] = 0; np[s] = 0u; }
+    const uint32_t one = (uint32_t)P.one;
+
+    if (tiled) {
+        const uint32_t row_vec = (uint32_t)row_vec64;
+        const uint32_t row_elems = row_vec * kEPP;
+        const uint32_t row_bytes = row_vec * 16u;
+        const uint32_t tile_ticks = row_vec == 0 ? kGsMaxTileTicks : min(kGsMaxTileTicks, kStageVec / row_vec);
+        const uint32_t n_tiles = (T + tile_ticks - 1) / tile_ticks;
+        const uint32_t n_own = (uint32_t)(q1 - q0);
+        const uint32_t j0 = valid ? (uint32_t)(q0 - a0) : 0u;             // place inside the staged run
+        // all lanes of the warp own groups of one size: the loop over queues is unrolled for it
+        const uint32_t n_first = __shfl_sync(0xFFFFFFFFu, n_own, 0);
+        const bool uniform = __all_sync(0xFFFFFFFFu, valid && n_own == n_first);
+        auto stage = [&](uint32_t k) {
+            if (tid == 0 && k < n_tiles) {
+                const uint32_t t0 = k * tile_ticks;
+                const uint32_t nt = min(tile_ticks, T - t0);
+                uint64_t *bar = &bars[k % kGsStages];
+                int4 *dl = gsm + (k % kGsStages) * kArrays * kStageVec;
+                int4 *di = dl + kStageVec;
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // earlier reads of this buffer are done
+                mbar_expect_tx(bar, nt * row_bytes * kArrays);
+                if (row_bytes) {
+                    for (uint32_t t = 0; t < nt; ++t) {
+                        const uint64_t g = (uint64_t)(t0 + t) * Q + a0;
+                        bulk_copy_g2s(dl + t * row_vec, static_cast<const E *>(P.llen) + g, row_bytes, bar);
+                        if (IPMODE == 2) bulk_copy_g2s(di + t * row_vec, static_cast<const E *>(P.inprog) + g, row_bytes, bar);
+                    }
+                }
+            }
+        };
+        stage(0);
+        stage(1);
+        for (uint32_t k = 0; k < n_tiles; ++k) {
+            mbar_wait(&bars[k % kGsStages], (k / kGsStages) & 1u);       // tile k has landed
+            __syncthreads();                                              // all are done with tile k-1
+            stage(k + 2);                                                 // refill the buffer tile k-1 occupied
+            if (!valid) continue;
+            const uint32_t t0 = k * tile_ticks;
+            const uint32_t nt = min(tile_ticks, T - t0);
+            const E *tl = reinterpret_cast<const E *>(gsm + (k % kGsStages) * kArrays * kStageVec) + j0;
+            const E *ti = tl + (size_t)kStageVec * kEPP;
+            const int32_t *iq = s_ipq + j0;
+            // the exact form of one tick (a count outside [0, 2^16) was seen)
+            auto slow_tick = [&](const E *lrow, const E *irow, int32_t (&want)[SP]) {
+                long long sum[SP];
+#pragma unroll
+                for (int s = 0; s < SP; ++s) sum[s] = 0;
+                for (uint32_t j = 0; j < n_own; ++j) {
+                    const int32_t l = (int32_t)lrow[j];
+                    const int32_t ip = IPMODE == 2 ? (int32_t)irow[j] : (IPMODE == 1 ? iq[j] : 0);
+#pragma unroll
+                    for (int s = 0; s < SP; ++s) sum[s] += decide_exact(l, ip, pol[s], cur[s]);   // autoscaler.py:255-257
+                }
+#pragma unroll
+                for (int s = 0; s < SP; ++s) want[s] = clip64(sum[s], pol[s].mn, pol[s].mx, cur[s]);   // :259
+            };
+            auto run_tile = [&](auto ntag) {
+                constexpr int N = decltype(ntag)::value;                  // queues per resource, 0: not known here
+                for (uint32_t t = 0; t < nt; ++t) {
+                    const E *lrow = tl + (size_t)t * row_elems;
+                    const E *irow = ti + (size_t)t * row_elems;
+                    uint32_t sum[SP];
+#pragma unroll
+                    for (int s = 0; s < SP; ++s) sum[s] = 0u;
+                    uint32_t any = 0u;
+                    auto one_queue = [&](uint32_t j) {
+                        uint32_t tally = (uint32_t)lrow[j];
+                        if constexpr (kCheck) any |= tally;
+                        if constexpr (IPMODE == 1) tally += (uint32_t)iq[j];          // range-checked when staged
+                        if constexpr (IPMODE == 2) {
+                            const uint32_t ip = (uint32_t)irow[j];
+                            if constexpr (kCheck) any |= ip;
+                            tally += ip;
+                        }
+#pragma unroll
+                        for (int s = 0; s < SP; ++s) {
+                            const uint32_t q = K1 ? tally : quotient_small(tally + 1u, pol[s]);
+                            sum[s] += (uint32_t)finish_simple3(q, keep_factor(q, keep[s], one), pol[s], cur[s]);   // :255-257
+                        }
+                    };
+                    if constexpr (N > 0) {
+#pragma unroll
+                        for (int j = 0; j < N; ++j) one_queue((uint32_t)j);
+                    } else {
+                        for (uint32_t j = 0; j < n_own; ++j) one_queue(j);
+                    }
+                    int32_t want[SP];
+                    if (kCheck && any >= kSmallTallyTerm) {
+                        slow_tick(lrow, irow, want);
+                    } else {
+#pragma unroll
+                        for (int s = 0; s < SP; ++s)                                                        // :259
+                            want[s] = finish_simple3(sum[s], keep_factor(sum[s], keep[s], one), pol[s], cur[s]);
+                    }
+#pragma unroll
+                    for (int s = 0; s < SP; ++s) {
+                        count_if_ne(np[s], want[s], cur[s]);                                                // :227
+                        cur[s] = want[s];
+                        pt[s] += want[s];
+                    }
+                }
+            };
+            if (SP == 1 && uniform) {
+                switch (n_first) {
+                    case 1: run_tile(std::integral_constant<int, 1>{}); break;
+                    case 2: run_tile(std::integral_constant<int, 2>{}); break;
+                    case 3: run_tile(std::integral_constant<int, 3>{}); break;
+                    case 4: run_tile(std::integral_constant<int, 4>{}); break;
+                    case 5: run_tile(std::integral_constant<int, 5>{}); break;
+                    case 6: run_tile(std::integral_constant<int, 6>{}); break;
+                    case 7: run_tile(std::integral_constant<int, 7>{}); break;
+                    case 8: run_tile(std::integral_constant<int, 8>{}); break;
+                    default: run_tile(std::integral_constant<int, 0>{}); break;
+                }
+            } else {
+                run_tile(std::integral_constant<int, 0>{});
+            }
+        }
+    } else if (valid) {
+        // element-wise loads, exact arithmetic: any offsets, any group size
+        const int32_t *iqg = static_cast<const int32_t *>(P.inprog);
+        for (uint32_t t = 0; t < T; ++t) {
+            const E *lrow = static_cast<const E *>(P.llen) + (uint64_t)t * Q;
+            const E *irow = static_cast<const E *>(P.inprog) + (uint64_t)t * Q;
+            long long sum[SP];
+#pragma unroll
+            for (int s = 0; s < SP; ++s) sum[s] = 0;
+            for (uint64_t q = q0; q < q1; ++q) {
+                const int32_t l = ld_trace_cached<E>(lrow + q);
+                const int32_t ip = IPMODE == 2 ? ld_trace_cached<E>(irow + q) : (IPMODE == 1 ? __ldg(iqg + q) : 0);
+#pragma unroll
+                for (int s = 0; s < SP; ++s) sum[s] += decide_exact(l, ip, pol[s], cur[s]);
+            }
+#pragma unroll
+            for (int s = 0; s < SP; ++s) {
+                const int32_t want = clip64(sum[s], pol[s].mn, pol[s].mx, cur[s]);
+                count_if_ne(np[s], want, cur[s]);
+                cur[s] = want;
+                pt[s] += want;
+            }
+        }
+    }
+    if (valid && P.totals) {
+#pragma unroll
+        for (int s = 0; s < SP; ++s)
+            if (live[s]) {
+                kas_totals o;
+                o.pod_ticks = pt[s];
+                o.n_patches = np[s];
+                o.final_current = cur[s];
+                P.totals[r * P.S + P.pol_index[pbase + s]] = o;
+            }
+    }
+    if (P.sums) {
+#pragma unroll
+        for (int s = 0; s < SP; ++s) {
+            if (live[s]) {
+                long long a = valid ? pt[s] : 0, b = valid ? (long long)np[s] : 0, c = valid ? (long long)cur[s] : 0;
+                a = warp_sum_ll(a); b = warp_sum_ll(b); c = warp_sum_ll(c);
+                if ((tid & 31u) == 0) {
+                    unsigned long long *o = P.sums + 3ull * P.pol_index[pbase + s];
+                    atomicAdd(o + 0, (unsigned long long)a);
+                    atomicAdd(o + 1, (unsigned long long)b);
+                    atomicAdd(o + 2, (unsigned long long)c);
+                }
+            }
+        }
+    }
+}
+
 template <typename E, int VEC, int SP>
 static void launch_identity(const ReplayParams &P, int mode, cudaStream_t stream) {
     const uint64_t threads = (P.R + VEC - 1) / VEC;
@@ -1309,6 +1610,38 @@ static int launch_grouped(const ReplayParams &P, int mode, cudaStream_t stream) 
     const bool tickip = P.inprog_mode == 2;
     const bool tileable = P.group_off != nullptr && P.Q % kEPP == 0 && aligned(P.llen, 16) &&
                           (!tickip || aligned(P.inprog, 16));
+    // realistic policies and nothing exotic asked for: the lean kernel (sorted threads, TMA tiles)
+    bool lean = tileable && mode != kGeneric && !P.cur0 && !P.patch_fail && !P.dense;
+    for (uint32_t s = 0; s < P.pol_count && lean; ++s)
+        lean = P.pol[s].m32 != 0u && P.pol[s].mx < kGsMaxPods;
+#ifdef KAS_NO_LEAN_GROUPED
+    lean = false;
+#endif
+    if (lean) {
+        const bool k1 = SP == 1 && P.pol[0].k1 != 0u;
+        const size_t smem = (size_t)kGsStages * (tickip ? 2 : 1) * kGsStageBytes +
+                            (P.inprog_mode == 1 ? (size_t)kGsStageBytes / sizeof(E) * 4 : 0);
+#define KAS_LAUNCH_GS(IPM, KONE)                                                                   \
+    do {                                                                                           \
+        auto kern = replay_grouped_sorted_kernel<E, SP, IPM, KONE>;                                \
+        KAS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
+                                          (int)smem));                                             \
+        kern<<<grid, kGsThreads, smem, stream>>>(P);                                               \
+    } while (0)
+        if constexpr (SP == 1) {
+            if (k1) {
+                if (P.inprog_mode == 0) KAS_LAUNCH_GS(0, true);
+                else if (P.inprog_mode == 1) KAS_LAUNCH_GS(1, true);
+                else KAS_LAUNCH_GS(2, true);
+                return KAS_OK;
+            }
+        }
+        if (P.inprog_mode == 0) KAS_LAUNCH_GS(0, false);
+        else if (P.inprog_mode == 1) KAS_LAUNCH_GS(1, false);
+        else KAS_LAUNCH_GS(2, false);
+#undef KAS_LAUNCH_GS
+        return KAS_OK;
+    }
     if (tileable) {
         const size_t smem = (size_t)kGroupedStages * (tickip ? 2 : 1) * kGroupedTileBytes;
 #define KAS_LAUNCH_GT(MD, TI)                                                                      \

@@ -47,6 +47,12 @@ def lib():
                                             C.c_void_p, C.c_int]
         L.kas_oracle_trace_fill.restype = None
         L.kas_oracle_max_threads.restype = C.c_int
+        L.kas_oracle_synth_heads.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p,
+                                             C.c_uint32, C.c_int, C.c_uint32, C.c_void_p, C.c_int]
+        L.kas_oracle_synth_heads.restype = None
+        L.kas_oracle_synth_blob.argtypes = [C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p,
+                                            C.c_uint32, C.c_int, C.c_void_p, C.c_void_p, C.c_int]
+        L.kas_oracle_synth_blob.restype = C.c_uint64
         _lib = L
     return _lib
 
@@ -148,3 +154,33 @@ def trace_fill(seed, T, q_first, n_q, threads=None):
     out = np.empty((T, n_q), dtype=np.int32)
     lib().kas_oracle_trace_fill(seed, T, q_first, n_q, out.ctypes.data, threads or max_threads())
     return out
+
+
+def rec_bytes_for(queues):
+    """Record width the path uses for these names: "processing-" + name + ":" rounded up to 16."""
+    longest = max((len(q if isinstance(q, bytes) else q.encode('utf-8')) for q in queues), default=0)
+    return 16 * ((11 + longest + 1 + 15) // 16)
+
+
+def synth_heads(seed, first_key, n_keys, queues, rec_bytes, long_tail=False, threads=None):
+    """The synthetic keyspace of DESIGN.md section 5 as packed heads, made by the oracle's own
+    generator (no product code involved)."""
+    names, noff = _names_blob(queues)
+    out = np.empty((n_keys, rec_bytes), dtype=np.uint8)
+    lib().kas_oracle_synth_heads(seed, first_key, n_keys, names.ctypes.data, noff.ctypes.data,
+                                 len(queues), int(long_tail), rec_bytes, out.ctypes.data,
+                                 threads or max_threads())
+    return out
+
+
+def synth_blob(seed, first_key, n_keys, queues, long_tail=False, threads=None):
+    """The same keys as (blob uint8, offsets uint64 [n+1])."""
+    names, noff = _names_blob(queues)
+    off = np.empty(n_keys + 1, dtype=np.uint64)
+    t = threads or max_threads()
+    need = lib().kas_oracle_synth_blob(seed, first_key, n_keys, names.ctypes.data, noff.ctypes.data,
+                                       len(queues), int(long_tail), None, off.ctypes.data, t)
+    blob = np.empty(max(1, need), dtype=np.uint8)
+    lib().kas_oracle_synth_blob(seed, first_key, n_keys, names.ctypes.data, noff.ctypes.data,
+                                len(queues), int(long_tail), blob.ctypes.data, off.ctypes.data, t)
+    return blob[:need], off

@@ -285,6 +285,128 @@ KAS_EXPORT void kas_oracle_trace_fill(uint64_t seed, uint32_t T, uint64_t q_firs
             out[(uint64_t)t * n_q + j] = kas_oracle_trace_value(seed, q_first + j, t);
 }
 
+/* ---- Twin of the library's synthetic keyspace generator ------------------
+ * Restated from the written spec, so that the CPU arm
+ * of the bench and the tests can make their inputs without loading the product
+ * library.  Key i of a keyspace (seed, names, long_tail):
+ *   h0 = mix64(seed ^ mix64(i)); h1 = mix64(h0); cls = h0 % 100;
+ *   name = names[(h0 >> 8) % n]; sl = (h0 >> 32) % 25
+ *          (+ (h1 >> 8) % 680 when long_tail and (h1 & 0xFF) < 13);
+ *   suffix char k = alphabet64[(mix64(h1 + k/10) >> 6*(k%10)) & 63].          */
+#define KAS_ORACLE_KEY_CAP 4096
+static const char kas_alphabet64[65] =
+    "0123456789abcdefghijklmnopqrstuvwxyzABCDEFGHIJKLMNOPQRSTUVWXYZ-:";
+
+static uint32_t put_bytes(uint8_t *out, uint32_t at, const void *src, uint32_t n)
+{
+    if (at + n > KAS_ORACLE_KEY_CAP) n = KAS_ORACLE_KEY_CAP - at;
+    memcpy(out + at, src, n);
+    return at + n;
+}
+
+static uint32_t put_suffix(uint8_t *out, uint32_t at, uint64_t h1, uint32_t sl)
+{
+    uint64_t word = 0;
+    for (uint32_t k = 0; k < sl && at < KAS_ORACLE_KEY_CAP; ++k) {
+        if (k % 10 == 0) word = mix64(h1 + k / 10);
+        out[at++] = (uint8_t)kas_alphabet64[(word >> (6 * (k % 10))) & 63u];
+    }
+    return at;
+}
+
+/* Writes key i into out (capacity KAS_ORACLE_KEY_CAP) and returns its length. */
+static uint32_t synth_key(uint64_t seed, uint64_t i, const uint8_t *names, const uint32_t *name_off,
+                          uint32_t n_names, int long_tail, uint8_t *out)
+{
+    const uint64_t h0 = mix64(seed ^ mix64(i));
+    const uint64_t h1 = mix64(h0);
+    const uint32_t cls = (uint32_t)(h0 % 100u);
+    const uint32_t j = (uint32_t)((h0 >> 8) % n_names);
+    uint32_t sl = (uint32_t)((h0 >> 32) % 25u);
+    if (long_tail && (h1 & 0xFFu) < 13u) sl += (uint32_t)((h1 >> 8) % 680u);
+    const uint8_t *nm = names + name_off[j];
+    const uint32_t nl = name_off[j + 1] - name_off[j];
+    uint32_t at = 0;
+    if (cls < 50) {            /* processing-<name>:<suffix>      counts for <name> */
+        at = put_bytes(out, at, "processing-", 11); at = put_bytes(out, at, nm, nl);
+        at = put_bytes(out, at, ":", 1); at = put_suffix(out, at, h1, sl);
+    } else if (cls < 56) {     /* processing-<name>x:<suffix>     near miss */
+        at = put_bytes(out, at, "processing-", 11); at = put_bytes(out, at, nm, nl);
+        at = put_bytes(out, at, "x:", 2); at = put_suffix(out, at, h1, sl);
+    } else if (cls < 61) {     /* processing-<name>               no colon */
+        at = put_bytes(out, at, "processing-", 11); at = put_bytes(out, at, nm, nl);
+    } else if (cls < 66) {     /* xprocessing-<name>:<suffix> */
+        at = put_bytes(out, at, "xprocessing-", 12); at = put_bytes(out, at, nm, nl);
+        at = put_bytes(out, at, ":", 1); at = put_suffix(out, at, h1, sl);
+    } else if (cls < 71) {     /* processing-<name minus last byte>:<suffix> */
+        at = put_bytes(out, at, "processing-", 11); at = put_bytes(out, at, nm, nl ? nl - 1 : 0);
+        at = put_bytes(out, at, ":", 1); at = put_suffix(out, at, h1, sl);
+    } else if (cls < 74) {     /* <name>                          the queue's own list key */
+        at = put_bytes(out, at, nm, nl);
+    } else if (cls < 77) {     /* processing-<name>:              empty suffix, matches */
+        at = put_bytes(out, at, "processing-", 11); at = put_bytes(out, at, nm, nl);
+        at = put_bytes(out, at, ":", 1);
+    } else if (cls < 80) {     /* Processing-<name>:<suffix>      case differs */
+        at = put_bytes(out, at, "Processing-", 11); at = put_bytes(out, at, nm, nl);
+        at = put_bytes(out, at, ":", 1); at = put_suffix(out, at, h1, sl);
+    } else {                   /* <name>:<suffix>:<hex16(h1)>     a job hash */
+        static const char hexd[] = "0123456789abcdef";
+        at = put_bytes(out, at, nm, nl); at = put_bytes(out, at, ":", 1);
+        at = put_suffix(out, at, h1, sl); at = put_bytes(out, at, ":", 1);
+        for (int k = 0; k < 16 && at < KAS_ORACLE_KEY_CAP; ++k) out[at++] = (uint8_t)hexd[(h1 >> (4 * k)) & 15u];
+    }
+    return at;
+}
+
+/* Keys first_key .. first_key+n_keys-1 as zero-padded heads of rec_bytes. */
+KAS_EXPORT void kas_oracle_synth_heads(uint64_t seed, uint64_t first_key, uint64_t n_keys,
+                                       const uint8_t *names, const uint32_t *name_off,
+                                       uint32_t n_names, int long_tail, uint32_t rec_bytes,
+                                       uint8_t *out_heads, int threads)
+{
+#pragma omp parallel num_threads(threads > 0 ? threads : 1)
+    {
+        uint8_t key[KAS_ORACLE_KEY_CAP];
+#pragma omp for schedule(static)
+        for (uint64_t i = 0; i < n_keys; ++i) {
+            uint32_t len = synth_key(seed, first_key + i, names, name_off, n_names, long_tail, key);
+            uint32_t n = len < rec_bytes ? len : rec_bytes;
+            memcpy(out_heads + i * rec_bytes, key, n);
+            memset(out_heads + i * rec_bytes + n, 0, rec_bytes - n);
+        }
+    }
+}
+
+/* The same keys as a blob + offsets.  out_off [n_keys+1] is always written;
+ * out_blob may be NULL to size the blob (returns the bytes needed).          */
+KAS_EXPORT uint64_t kas_oracle_synth_blob(uint64_t seed, uint64_t first_key, uint64_t n_keys,
+                                          const uint8_t *names, const uint32_t *name_off,
+                                          uint32_t n_names, int long_tail,
+                                          uint8_t *out_blob, uint64_t *out_off, int threads)
+{
+#pragma omp parallel num_threads(threads > 0 ? threads : 1)
+    {
+        uint8_t key[KAS_ORACLE_KEY_CAP];
+#pragma omp for schedule(static)
+        for (uint64_t i = 0; i < n_keys; ++i)
+            out_off[i + 1] = synth_key(seed, first_key + i, names, name_off, n_names, long_tail, key);
+    }
+    out_off[0] = 0;
+    for (uint64_t i = 0; i < n_keys; ++i) out_off[i + 1] += out_off[i];
+    if (out_blob) {
+#pragma omp parallel num_threads(threads > 0 ? threads : 1)
+        {
+            uint8_t key[KAS_ORACLE_KEY_CAP];
+#pragma omp for schedule(static)
+            for (uint64_t i = 0; i < n_keys; ++i) {
+                uint32_t len = synth_key(seed, first_key + i, names, name_off, n_names, long_tail, key);
+                memcpy(out_blob + out_off[i], key, len);
+            }
+        }
+    }
+    return out_off[n_keys];
+}
+
 KAS_EXPORT int kas_oracle_max_threads(void)
 {
 #ifdef _OPENMP

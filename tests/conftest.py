@@ -40,10 +40,10 @@ def _built():
     spec = importlib.util.spec_from_file_location('kas_build', os.path.join(PKG, 'build.py'))
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
-    if not os.path.exists(mod.OUT) or os.path.exists('/usr/local/cuda/bin/nvcc'):
-        try:
-            mod.build()
-        except Exception:
-            if not os.path.exists(mod.OUT):
-                raise
+    if os.path.exists(mod.NVCC):
+        mod.build()          # no-op when the library is newer than its sources; a failing nvcc fails the session
+    elif not os.path.exists(mod.OUT):
+        raise RuntimeError('libkas.so is missing and there is no nvcc to build it')
+    elif mod._stale():
+        raise RuntimeError('libkas.so is older than its sources and there is no nvcc to rebuild it')
     yield

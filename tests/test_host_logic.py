@@ -107,6 +107,24 @@ def test_synthetic_keys_are_deterministic_and_sliceable():
     assert 0.55 < starts.mean() < 0.8
 
 
+def test_keyspace_generator_twin_in_the_oracle():
+    """The oracle's own generator (written from the spec in DESIGN.md) makes the keys the
+    library's generator makes: heads, blob and offsets, plain and long-tailed, any start."""
+    from autoscaler import engine
+    from oracle import coracle
+    names = helpers.c2_queue_names(64)
+    assert coracle.rec_bytes_for(names) == engine.rec_bytes_for(names) == 32
+    for long_tail in (False, True):
+        h, b, o = engine.synth_keys_host(11, 123456789, 6000, names, long_tail=long_tail, rec_bytes=32,
+                                         want_blob=True)
+        assert (coracle.synth_heads(11, 123456789, 6000, names, 32, long_tail=long_tail) == h).all()
+        b2, o2 = coracle.synth_blob(11, 123456789, 6000, names, long_tail=long_tail)
+        assert (o2 == o).all() and (b2 == b).all()
+    few = ['a', 'predict:zstack']
+    h, _, _ = engine.synth_keys_host(3, 0, 999, few, rec_bytes=48)
+    assert (coracle.synth_heads(3, 0, 999, few, 48, threads=1) == h).all()
+
+
 def test_package_surface_and_init_parsing():
     import autoscaler
     assert autoscaler.Autoscaler and autoscaler.redis.RedisClient
@@ -249,6 +267,102 @@ def test_redis_client_routing_and_retries(monkeypatch):
     monkeypatch.setattr(mod.StrictRedis, 'sentinel_masters', no_sentinel)
     c2 = autoscaler.redis.RedisClient(host='plain', port=6379)
     assert c2._redis_master is c2._sentinel and c2._redis_slaves == [c2._sentinel]
+
+
+def test_tally_queues_through_redis_client(monkeypatch):
+    """The live loop of scale.py hands Autoscaler a RedisClient, whose __getattr__ answers ANY
+    attribute name with a command wrapper: the snapshot seam must not be mistaken for present
+    (it would forward `key_snapshot` to the server and die on the first tick).  The tally must
+    take ONE scan of the keyspace through scan_iter instead."""
+    import autoscaler
+    mod, state = _fake_redis_module()
+    monkeypatch.setitem(sys.modules, 'redis', mod)
+    monkeypatch.setitem(sys.modules, 'redis.exceptions', mod.exceptions)
+    client = autoscaler.redis.RedisClient(host='sentinel', port=26379, backoff=0)
+    assert callable(getattr(client, 'key_snapshot', None))        # the trap
+    seen = {}
+
+    def fake_tally(snapshot, names, device='cuda'):
+        seen['keys'] = [bytes(snapshot.blob[snapshot.off[i]:snapshot.off[i + 1]])
+                        for i in range(len(snapshot))]
+        return [3] * len(names)
+    monkeypatch.setattr(autoscaler.snapshot, 'tally_snapshot', fake_tally)
+    scaler = autoscaler.Autoscaler(client, 'predict,track')
+    scaler.tally_queues()
+    assert seen['keys'] == [b'master']                            # scan_iter went to the master
+    assert scaler.redis_keys == {'predict': 7 + 3, 'track': 7 + 3}   # llen from a replica + scan term
+    # the offline stand-in still short-cuts the scan
+    snap = autoscaler.snapshot.KeySnapshot.from_keys([b'processing-predict:a'])
+    scaler2 = autoscaler.Autoscaler(autoscaler.snapshot.SnapshotRedis(snap, {'predict': 1}), 'predict')
+    scaler2.tally_queues()
+    assert seen['keys'] == [b'processing-predict:a'] and scaler2.redis_keys == {'predict': 4}
+
+
+def test_scale_honours_an_overridden_get_desired_pods(monkeypatch):
+    """Reference scale() calls self.get_desired_pods once per key (autoscaler.py:254-257), so a
+    subclass or a patched instance method takes part in the decision; the batched launch is
+    only used when the method is the stock one."""
+    import autoscaler
+    from autoscaler import engine
+    calls = []
+
+    def fake_decide(a, kpp, mn, mx, cur, mode=0):
+        calls.append(mode)
+        return [0] * len(a)
+    monkeypatch.setattr(engine, 'decide', fake_decide)
+    monkeypatch.setattr(autoscaler.snapshot, 'tally_snapshot', lambda snap, names, device='cuda': [0] * len(names))
+
+    class Mine(autoscaler.Autoscaler):
+        def get_desired_pods(self, key, keys_per_pod, min_pods, max_pods, current_pods):
+            return {'a': 2, 'b': 5}[key]
+
+        def get_current_pods(self, *a, **k):
+            return 1
+    seen = []
+    s = Mine(autoscaler.snapshot.SnapshotRedis(), 'a,b')
+    s.clip_pod_count = lambda d, mn, mx, cur: seen.append(d) or d
+    s.scale_resource = lambda *a: None
+    s.scale('ns', 'deployment', 'x')
+    assert seen == [7] and calls == []                  # per-key calls, no batched launch
+    t = autoscaler.Autoscaler(autoscaler.snapshot.SnapshotRedis(), 'a,b')
+    t.get_current_pods = lambda *a, **k: 1
+    t.get_desired_pods = lambda key, *a: 4              # patched on the instance, as the reference's tests do
+    t.clip_pod_count = lambda d, mn, mx, cur: seen.append(d) or d
+    t.scale_resource = lambda *a: None
+    t.scale('ns', 'deployment', 'x')
+    assert seen == [7, 8] and calls == []
+    u = autoscaler.Autoscaler(autoscaler.snapshot.SnapshotRedis(), 'a,b')
+    u.get_current_pods = lambda *a, **k: 1
+    u.clip_pod_count = lambda d, mn, mx, cur: d
+    u.scale_resource = lambda *a: None
+    u.scale('ns', 'deployment', 'x')
+    assert calls == [0]                                 # the stock method: one batched launch
+
+
+def test_api_exception_subclasses_are_swallowed_like_the_reference():
+    """`except ApiException` (reference autoscaler.py:267) also catches subclasses."""
+    import autoscaler
+    from tests import helpers
+
+    class Conflict(helpers.ApiException):
+        pass
+    s = autoscaler.Autoscaler(autoscaler.snapshot.SnapshotRedis(), 'a')
+    s.tally_queues = lambda: None
+    s.get_current_pods = lambda *a, **k: 0
+    s._get_desired_pods_is_stock = lambda: False
+    s.get_desired_pods = lambda *a: 1
+    s.clip_pod_count = lambda d, mn, mx, cur: d
+
+    def boom(*a):
+        raise Conflict('409')
+    s.scale_resource = boom
+    s.scale('ns', 'deployment', 'x')                    # swallowed
+
+    def boom2(*a):
+        raise KeyError('other')
+    s.scale_resource = boom2
+    with pytest.raises(KeyError):
+        s.scale('ns', 'deployment', 'x')
 
 
 def test_scale_py_config(monkeypatch):
