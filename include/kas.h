@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define KAS_VERSION 101 /* 0.1.1: kas_replay_args.startup_delay */
+#define KAS_VERSION 102 /* 0.1.2: kas_comm_*, kas_allreduce_i64 */
 
 #if defined(__GNUC__)
 #define KAS_API __attribute__((visibility("default")))
@@ -289,6 +289,37 @@ KAS_API int kas_patch_event_emit(const kas_replay_args *args, uint32_t policy_in
                                  const uint64_t *d_event_off, kas_patch_event *d_events,
                                  uint64_t capacity, void *stream);
 
+/* ------------------------------------------------------------------------
+ * Time to the first pod after a burst: the third number of a policy report,
+ * beside pod-hours (cost) and patch count (churn).  The reference computes
+ * none of them; README.md:7 names the purpose ("minimizing GPU costs").  Same
+ * inputs, domain and policy handling as kas_patch_event_offsets (one policy,
+ * args->policies[policy_index]; patch_fail and startup_delay honoured).
+ *
+ * Per resource, over the replayed scale loop (autoscaler.py:244-273):
+ *   - a burst STARTS on a tick whose tally (sum over the resource's queues of
+ *     LLEN + SCAN count, autoscaler.py:73) is > 0 after a tick where it was
+ *     <= 0 (before tick 0 it counts as 0), if the controller reads <= 0 pods on
+ *     that tick (autoscaler.py:252; the available ones when startup_delay > 0,
+ *     :176-177) and no earlier burst is still waiting;
+ *   - it is SERVED on the first tick, at or after its start, after which pods
+ *     run (the next tick would read > 0): wait = that tick - starting tick;
+ *   - it went UNSERVED if the tally is back at <= 0 before that.
+ * d_out [R] (or NULL); d_sums int64 [5] (or NULL): sum n_served, sum
+ * n_unserved, sum wait_sum, MAX wait_max, sum pending.
+ * ---------------------------------------------------------------------- */
+typedef struct kas_first_pod {
+    uint32_t n_served;   /* bursts that got their first pod                     */
+    uint32_t n_unserved; /* bursts whose work left before a pod ran             */
+    uint32_t wait_max;   /* longest wait of a served burst, in ticks            */
+    uint32_t pending;    /* ticks the last burst has waited when the trace ends */
+    uint64_t wait_sum;   /* sum of the waits of served bursts, in ticks         */
+} kas_first_pod;
+
+KAS_API int kas_first_pod_latency(const kas_replay_args *args, uint32_t policy_index,
+                                  kas_first_pod *d_out /* [R] or NULL */,
+                                  int64_t *d_sums /* [5] or NULL */, void *stream);
+
 /* kas_patch_event_offsets without a scratch buffer from the caller.
  * (No counterpart in the reference, which never touches a GPU.)
  *
@@ -321,6 +352,33 @@ KAS_API int kas_patch_event_emit(const kas_replay_args *args, uint32_t policy_in
 #define KAS_STATIC_SCRATCH_MAX_RESOURCES 33554432ull /* 8192 scan tiles of 4096 */
 KAS_API int kas_patch_event_offsets_static(const kas_replay_args *args, uint32_t policy_index,
                                            uint64_t *d_event_off /* [R+1] */, void *stream);
+
+/* ------------------------------------------------------------------------
+ * Box-wide totals: the single collective of the path.
+ * Keys (kas_match_count) and resources (kas_replay) are split over the GPUs of
+ * a box by contiguous range with no exchange on the data path; afterwards one
+ * all-reduce(sum) makes every rank hold what ONE Autoscaler would have seen:
+ * the uint64 [Q] counts behind redis_keys (autoscaler.py:60-77) and the int64
+ * [S][3] sums of the replayed scale loop (autoscaler.py:244-260).  Integer
+ * sums do not depend on the order, so the result is the same bits at every
+ * world size.  One process per GPU; NCCL is bound at run time (dlopen), and
+ * without it these calls return KAS_ERR_UNSUPPORTED.
+ *
+ *   rank 0:     kas_comm_unique_id(id)        then hand `id` to every rank
+ *                                             (any side channel: a file, a
+ *                                             TCP store, torch.distributed)
+ *   every rank: kas_comm_init(&comm, n_ranks, rank, id)   with its GPU current
+ *               kas_allreduce_i64(comm, d_buf, n, stream) in place, async on
+ *                                             the stream; uint64 counts are
+ *                                             reduced as int64 (same bits)
+ *               kas_comm_destroy(comm)
+ * The communicators are the library's only long-lived global state.
+ * ---------------------------------------------------------------------- */
+#define KAS_COMM_ID_BYTES 128
+KAS_API int kas_comm_unique_id(uint8_t *id /* [KAS_COMM_ID_BYTES] */);
+KAS_API int kas_comm_init(void **comm, int n_ranks, int rank, const uint8_t *id);
+KAS_API int kas_allreduce_i64(void *comm, int64_t *d_buf, size_t n, void *stream);
+KAS_API int kas_comm_destroy(void *comm);
 
 /* ------------------------------------------------------------------------
  * Synthetic workload generators (no counterpart in the reference, which has

@@ -48,15 +48,15 @@ class Autoscaler(object):
         self.managed_resource_types = {'deployment', 'job'}
 
     # ------------------------------------------------------------------ tally
-    def _take_snapshot(self):
+    def _scan_term(self, names):
+        """SCAN-count term of every queue: from the client's snapshot when it hands one out
+        (offline replay), else from ONE streamed scan of the live server."""
         # looked up on the CLASS: RedisClient.__getattr__ (reference redis.py:163-176) answers
         # every attribute name with a command wrapper, so an instance lookup proves nothing
         taker = getattr(type(self.redis_client), 'key_snapshot', None)
         if callable(taker):
-            return self.redis_client.key_snapshot()
-        # a live server: ONE scan for every queue instead of one per queue
-        return _snapshot.KeySnapshot.from_redis(self.redis_client, match='processing-*',
-                                                count=1000)
+            return _snapshot.tally_snapshot(self.redis_client.key_snapshot(), names)
+        return _snapshot.tally_live(self.redis_client, names, match='processing-*', count=1000)
 
     def tally_queues(self):
         """Update counts of all redis queues (reference autoscaler.py:60-77):
@@ -68,7 +68,7 @@ class Autoscaler(object):
         for q in names:
             self.logger.debug('Tallying items in queue `%s`.', q)
             waiting.append(self.redis_client.llen(q))
-        in_progress = _snapshot.tally_snapshot(self._take_snapshot(), names)
+        in_progress = self._scan_term(names)
         for q, num_items, num_in_progress in zip(names, waiting, in_progress):
             self.redis_keys[q] = num_items + num_in_progress
         self.logger.debug('Finished tallying redis keys in %s seconds.',

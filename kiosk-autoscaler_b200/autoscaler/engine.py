@@ -26,6 +26,7 @@ KAS_ERR_STATIC_LIMIT = -8
 TRACE_INT32 = 0
 TRACE_UINT16 = 1
 STATIC_SCRATCH_MAX_RESOURCES = 33554432
+COMM_ID_BYTES = 128
 
 MAX_PREFIXES = 1024
 MAX_REC_BYTES = 64
@@ -61,6 +62,8 @@ class Totals(C.Structure):
 
 
 EVENT_DTYPE = np.dtype([('tick', '<u4'), ('from_pods', '<i4'), ('to_pods', '<i4')])
+FIRST_POD_DTYPE = np.dtype([('n_served', '<u4'), ('n_unserved', '<u4'), ('wait_max', '<u4'), ('pending', '<u4'),
+                            ('wait_sum', '<u8')])
 TOTALS_DTYPE = np.dtype([('pod_ticks', '<i8'), ('n_patches', '<u4'), ('final_current', '<i4')])
 
 
@@ -119,6 +122,11 @@ SYMBOLS = {
                                                  C.c_void_p]),
     'kas_patch_event_emit': (C.c_int, [C.POINTER(ReplayArgs), C.c_uint32, C.c_void_p, C.c_void_p,
                                        C.c_uint64, C.c_void_p]),
+    'kas_first_pod_latency': (C.c_int, [C.POINTER(ReplayArgs), C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'kas_comm_unique_id': (C.c_int, [C.c_void_p]),
+    'kas_comm_init': (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_void_p]),
+    'kas_allreduce_i64': (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    'kas_comm_destroy': (C.c_int, [C.c_void_p]),
     'kas_synth_trace': (C.c_int, [C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint64, C.c_void_p,
                                   C.c_void_p]),
     'kas_synth_keys_host': (C.c_int, [C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p,
@@ -436,6 +444,33 @@ def patch_events(d_llen, n_ticks, n_queues, policy, d_inprog=None, inprog_mode=0
     return off.cpu().numpy().view(np.uint64), ev
 
 
+def first_pod_latency(d_llen, n_ticks, n_queues, policy, d_inprog=None, inprog_mode=0, d_group_off=None,
+                      n_resources=None, d_cur0=None, d_patch_fail=None, startup_delay=0, want_rows=True):
+    """Time to the first pod after a burst (kas_first_pod_latency) for one policy.  Returns
+    (rows, sums): rows a numpy structured array [R] (FIRST_POD_DTYPE) or None, sums int64 [5] =
+    served, unserved, wait_sum, max wait, pending."""
+    torch = require_cuda()
+    k, a, b = (int(v) for v in policy)
+    for v in (k, a, b):
+        if not -(2 ** 31) <= v < 2 ** 31:
+            raise OverflowError('policy values must fit in int32, got %r' % (policy,))
+    R = n_queues if n_resources is None else n_resources
+    parr = (Policy * 1)(Policy(k, a, b))
+    dev = d_llen.device
+    dt = trace_dtype_of(d_llen)
+    if inprog_mode == 2 and trace_dtype_of(d_inprog) != dt:
+        raise TypeError('a per-tick in-progress trace must have the element type of the LLEN trace')
+    args = ReplayArgs(ptr(d_llen), ptr(d_inprog), inprog_mode, n_ticks, n_queues, R,
+                      ptr(d_group_off), ptr(d_cur0), parr, 1, None, None, None, dt, ptr(d_patch_fail),
+                      _check_delay(startup_delay))
+    rows = torch.empty((R, FIRST_POD_DTYPE.itemsize), dtype=torch.uint8, device=dev) if want_rows else None
+    sums = torch.empty(5, dtype=torch.int64, device=dev)
+    check(lib().kas_first_pod_latency(C.byref(args), 0, ptr(rows), ptr(sums), stream_ptr()),
+          'kas_first_pod_latency')
+    host_rows = rows.cpu().numpy().reshape(-1).view(FIRST_POD_DTYPE) if want_rows else None
+    return host_rows, sums.cpu().numpy()
+
+
 def totals_to_host(d_totals):
     """uint8 [R][S][16] CUDA tensor -> numpy structured array [R][S]."""
     a = d_totals.cpu().numpy()
@@ -464,3 +499,53 @@ def device_info():
     a, b, c = C.c_int(0), C.c_int(0), C.c_int(0)
     check(lib().kas_device_info(C.byref(a), C.byref(b), C.byref(c)), 'kas_device_info')
     return dict(sm_count=a.value, cc=(b.value, c.value))
+
+
+# --------------------------------------------------------------------------
+# box-wide totals (the single collective of the path)
+# --------------------------------------------------------------------------
+class Comm(object):
+    """One rank's handle on the library's own communicator (kas_comm_* in include/kas.h):
+    an NCCL all-reduce of int64 totals issued by libkas on the caller's stream.  Torch is
+    not involved; any side channel may carry the 128-byte id from rank 0 to the others
+    (``Comm.from_torch_group`` uses an initialised torch.distributed group for that)."""
+
+    def __init__(self, world_size, rank, unique_id):
+        require_cuda()
+        uid = bytes(unique_id)
+        if len(uid) != COMM_ID_BYTES:
+            raise ValueError('the communicator id has %d bytes' % COMM_ID_BYTES)
+        self.world_size, self.rank = int(world_size), int(rank)
+        self._buf = C.create_string_buffer(uid, COMM_ID_BYTES)
+        self._comm = C.c_void_p(0)
+        check(lib().kas_comm_init(C.byref(self._comm), self.world_size, self.rank, self._buf),
+              'kas_comm_init')
+
+    @staticmethod
+    def unique_id():
+        buf = C.create_string_buffer(COMM_ID_BYTES)
+        check(lib().kas_comm_unique_id(buf), 'kas_comm_unique_id')
+        return buf.raw
+
+    @classmethod
+    def from_torch_group(cls, group=None):
+        """Every rank of an initialised torch.distributed group calls this (its GPU current)."""
+        import torch.distributed as dist
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        box = [cls.unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0,
+                                   group=group)
+        return cls(world, rank, box[0])
+
+    def allreduce_sum_(self, t):
+        """In-place sum over the ranks of an int64 CUDA tensor, on the current stream."""
+        torch = _torch()
+        if t.dtype != torch.int64 or not t.is_cuda or not t.is_contiguous():
+            raise TypeError('kas_allreduce_i64 takes a contiguous int64 CUDA tensor')
+        check(lib().kas_allreduce_i64(self._comm, ptr(t), t.numel(), stream_ptr()), 'kas_allreduce_i64')
+        return t
+
+    def destroy(self):
+        if self._comm:
+            check(lib().kas_comm_destroy(self._comm), 'kas_comm_destroy')
+            self._comm = C.c_void_p(0)

@@ -65,17 +65,25 @@ class ReplayResult(object):
         return out
 
 
-def sweep_report(result, interval_seconds=5, cost_per_pod_hour=1.0):
+def sweep_report(result, interval_seconds=5, cost_per_pod_hour=1.0, first_pod=None):
     """Per-policy summary of a replay: box-wide pod-hours (pod_ticks x INTERVAL / 3600,
     INTERVAL as in scale.py:84), cost, number of patch calls (churn) and whether the
     policy is on the cost / churn Pareto front.  All derived on the host from the
-    integer sums, so the report is identical at every world size."""
+    integer sums, so the report is identical at every world size.  ``first_pod``: the
+    list ``first_pod_latency`` returned for the same policies adds the responsiveness
+    columns (bursts served / unserved, mean and longest wait for the first pod)."""
     rows = []
-    for (kpp, mn, mx), s in zip(result.policies, result.sums):
+    for i, ((kpp, mn, mx), s) in enumerate(zip(result.policies, result.sums)):
         hours = int(s[0]) * interval_seconds / 3600.0
         rows.append(dict(keys_per_pod=kpp, min_pods=mn, max_pods=mx, pod_ticks=int(s[0]),
                          pod_hours=hours, cost=hours * cost_per_pod_hour, n_patches=int(s[1]),
                          final_pods=int(s[2])))
+        if first_pod is not None:
+            f = first_pod[i]
+            rows[-1].update(bursts_served=f['n_served'], bursts_unserved=f['n_unserved'],
+                            max_wait_ticks=f['wait_max'], mean_wait_ticks=f['mean_wait'],
+                            mean_wait_seconds=f['mean_wait'] * interval_seconds,
+                            bursts_pending=f['n_pending'])
     for a in rows:
         a['pareto'] = not any(
             (b['pod_ticks'] <= a['pod_ticks'] and b['n_patches'] <= a['n_patches'] and
@@ -108,7 +116,9 @@ def _to_device_trace(x, torch, what, like=None):
     if isinstance(x, torch.Tensor):
         if x.dtype not in (torch.int32, torch.uint16, torch.int16):
             raise TypeError('%s must be int32 or uint16' % what)
-        return x.contiguous().to('cuda')
+        x = x.contiguous()
+        # a pinned host tensor is copied asynchronously on the current stream
+        return x.to('cuda', non_blocking=x.device.type == 'cpu' and x.is_pinned())
     a = np.asarray(x)
     want_u16 = a.dtype == np.uint16 if like is None else like.dtype in (torch.uint16, torch.int16)
     if want_u16:
@@ -244,6 +254,72 @@ def patch_events(llen, policy, inprog=None, group_off=None, cur0=None, resource_
     return PatchLog(off, ev, resource_types)
 
 
+def first_pod_latency(llen, policies, inprog=None, group_off=None, cur0=None,
+                      resource_type='deployment', patch_fail=None, startup_delay=0, want_rows=False,
+                      comm=None):
+    """Time to the first pod after a burst, per policy, over a fleet (same inputs as
+    ``replay_fleet``; definition in include/kas.h).  Returns one dict per policy with the
+    box-wide integers n_served, n_unserved, wait_sum, wait_max, pending_ticks, n_pending (when
+    ``want_rows``), mean_wait (ticks) and, with ``want_rows``, ``rows`` (numpy structured [R]).
+    With a communicator / process group the sums are all-reduced (the maximum as a maximum)."""
+    _check_type(resource_type)
+    torch = engine.require_cuda()
+    d_llen = _to_device_trace(llen, torch, 'llen')
+    T, Q = int(d_llen.shape[0]), int(d_llen.shape[1])
+    if inprog is not None and np.ndim(inprog) == 2:
+        d_ip = _to_device_trace(inprog, torch, 'inprog', like=d_llen)
+    else:
+        d_ip = _to_device_i32(inprog, torch, 'inprog')
+    mode = 0 if d_ip is None else (1 if d_ip.dim() == 1 else 2)
+    d_go, R = None, Q
+    if group_off is not None:
+        go = np.ascontiguousarray(group_off, dtype=np.uint64)
+        if go[0] != 0 or go[-1] != Q or (np.diff(go.astype(np.int64)) < 0).any():
+            raise ValueError('group_off must rise from 0 to Q')
+        R = len(go) - 1
+        d_go = torch.from_numpy(go.view(np.int64)).to('cuda')
+    d_c0 = _to_device_i32(cur0, torch, 'cur0')
+    d_pf = _to_device_fail(patch_fail, torch, T, R)
+    delay = _delay_for(resource_type, startup_delay)
+    out = []
+    for pol in policies:
+        rows, sums = engine.first_pod_latency(d_llen, T, Q, pol, d_inprog=d_ip, inprog_mode=mode,
+                                              d_group_off=d_go, n_resources=R, d_cur0=d_c0,
+                                              d_patch_fail=d_pf, startup_delay=delay, want_rows=want_rows)
+        sums = _allreduce_first_pod(sums, comm)
+        served = int(sums[0])
+        d = dict(n_served=served, n_unserved=int(sums[1]), wait_sum=int(sums[2]), wait_max=int(sums[3]),
+                 pending_ticks=int(sums[4]), mean_wait=(int(sums[2]) / served) if served else 0.0,
+                 n_pending=int((rows['pending'] > 0).sum()) if rows is not None else None)
+        if want_rows:
+            d['rows'] = rows
+        out.append(d)
+    return out
+
+
+def _allreduce_first_pod(sums, comm):
+    """[served, unserved, wait_sum, max wait, pending]: four sums and one maximum over the ranks,
+    carried by ONE integer sum all-reduce (every rank puts its maximum in its own slot)."""
+    import torch
+    import torch.distributed as dist
+    if comm is not None:
+        world, rank, dev = comm.world_size, comm.rank, 'cuda'
+    elif dist.is_available() and dist.is_initialized():
+        world, rank = dist.get_world_size(), dist.get_rank()
+        dev = 'cuda' if dist.get_backend() == 'nccl' else 'cpu'
+    else:
+        world = 1
+    if world == 1:
+        return sums
+    v = np.zeros(4 + world, dtype=np.int64)
+    v[:4] = [sums[0], sums[1], sums[2], sums[4]]
+    v[4 + rank] = sums[3]
+    t = torch.from_numpy(v).to(dev)
+    allreduce_sum_(t, comm=comm)
+    v = t.cpu().numpy()
+    return np.array([v[0], v[1], v[2], v[4:].max(), v[3]], dtype=np.int64)
+
+
 def replay_one(queue_names, llen_trace, policies, inprog=None, current_pods=0,
                resource_type='deployment', managed=('deployment', 'job'), want_dense=False,
                patch_fail=None, startup_delay=0):
@@ -283,10 +359,14 @@ def shard_groups(group_off, rank, world_size):
     return r_lo, r_hi, q_lo, q_hi, (go[r_lo:r_hi + 1] - go[r_lo]).astype(np.uint64)
 
 
-def allreduce_sum_(t, group=None):
-    """Box-wide integer totals: one all-reduce (NCCL over NVLink for CUDA tensors,
-    gloo in the CPU tests).  Integer sums are order independent, so the result is
-    bit-exact at every world size.  No-op without an initialised process group."""
+def allreduce_sum_(t, group=None, comm=None):
+    """Box-wide integer totals: ONE all-reduce.  With ``comm`` (an ``engine.Comm``) libkas
+    issues the NCCL all-reduce itself on the current stream; otherwise torch.distributed
+    carries it (NCCL for CUDA tensors, gloo in the CPU tests).  Integer sums are order
+    independent, so the result is bit-exact at every world size.  No-op without a
+    communicator or an initialised process group."""
+    if comm is not None:
+        return comm.allreduce_sum_(t) if comm.world_size > 1 else t
     import torch.distributed as dist
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)

@@ -57,9 +57,10 @@ class KeySnapshot(object):
     @classmethod
     def from_redis(cls, redis_client, match='processing-*', count=1000):
         """One SCAN of a live server through any client exposing ``scan_iter``
-        (the RedisClient seam, redis.py:163-202 of the reference).  Only keys
-        that can match some ``processing-<q>:*`` are fetched."""
-        return cls.from_keys(list(redis_client.scan_iter(match=match, count=count)))
+        (the RedisClient seam, redis.py:163-202 of the reference), kept as a snapshot
+        object.  Only keys that can match some ``processing-<q>:*`` are fetched.  (The live
+        tally does not build this object: ``tally_live`` streams the scan to the GPU.)"""
+        return cls.from_keys(redis_client.scan_iter(match=match, count=count))
 
     # -- access -------------------------------------------------------------
     def __len__(self):
@@ -227,12 +228,168 @@ class StreamingTally(object):
         self.host_counts.copy_(self.counts, non_blocking=True)
         return self.host_counts
 
+    def plan_blob_chunks(self, off, blob_bytes_per_chunk):
+        """Key ranges [lo, hi) whose bytes fit one blob staging buffer and whose count fits
+        ``chunk_keys`` (host side, from the offsets of a blob + offsets snapshot)."""
+        off = np.ascontiguousarray(off, dtype=np.uint64)
+        n = len(off) - 1
+        out, lo = [], 0
+        while lo < n:
+            hi = int(np.searchsorted(off, off[lo] + np.uint64(blob_bytes_per_chunk), side='right')) - 1
+            hi = max(lo + 1, min(hi, n, lo + self.chunk_keys))
+            if int(off[hi] - off[lo]) > blob_bytes_per_chunk:
+                raise ValueError('a key of %d bytes does not fit the %d-byte staging buffer'
+                                 % (int(off[hi] - off[lo]), blob_bytes_per_chunk))
+            out.append((lo, hi))
+            lo = hi
+        return out
+
+    def enqueue_blob(self, host_blob, host_off, chunks, blob_bytes_per_chunk, sep_bytes=0, reduce=None):
+        """The same pipeline from the RAW snapshot: variable-length keys as a blob + uint64
+        offsets in (pinned) host memory.  Per chunk of keys the bytes and the offsets are
+        copied to the GPU, ``kas_pack_heads`` cuts the fixed-width heads there, and the match
+        kernel counts them; nothing is packed on the host.  ``chunks`` comes from
+        ``plan_blob_chunks``.  host_blob: uint8 tensor, host_off: int64-typed tensor [n+1]."""
+        torch = engine.require_cuda()
+        W = self.rec_bytes
+        if not hasattr(self, 'blob_stage') or self.blob_stage[0].numel() < blob_bytes_per_chunk + 16:
+            self.blob_stage = [torch.empty(blob_bytes_per_chunk + 16, dtype=torch.uint8, device=self.device)
+                               for _ in range(2)]
+            self.off_stage = [torch.empty(self.chunk_keys + 1, dtype=torch.int64, device=self.device)
+                              for _ in range(2)]
+        main = torch.cuda.current_stream(self.device)
+        self.counts.zero_()
+        for b in range(2):
+            self.free[b].record(main)
+        for i, (lo, hi) in enumerate(chunks):
+            b = i & 1
+            b0, b1 = int(host_off[lo]), int(host_off[hi])
+            with torch.cuda.stream(self.copy_stream):
+                self.copy_stream.wait_event(self.free[b])
+                self.blob_stage[b][:b1 - b0].copy_(host_blob[b0:b1], non_blocking=True)
+                self.off_stage[b][:hi - lo + 1].copy_(host_off[lo:hi + 1], non_blocking=True)
+                ready = torch.cuda.Event()
+                ready.record(self.copy_stream)
+            main.wait_event(ready)
+            # offsets stay absolute: the blob pointer is moved back by the chunk's first offset
+            # (only addresses inside the staging buffer are ever read)
+            engine.check(engine.lib().kas_pack_heads(
+                engine.C.c_void_p(self.blob_stage[b].data_ptr() - b0), engine.ptr(self.off_stage[b]),
+                hi - lo, sep_bytes, W, engine.ptr(self.stage[b]), engine.stream_ptr()), 'kas_pack_heads')
+            engine.match_count(self.stage[b], hi - lo, W, self.table, len(self.names),
+                               d_counts=self.counts, accumulate=True)
+            self.free[b].record(main)
+        self.launches += 2 * len(chunks)
+        if reduce is not None:
+            reduce(self.counts)
+        self.host_counts.copy_(self.counts, non_blocking=True)
+        return self.host_counts
+
     def run(self, host_heads, n_keys, reduce=None):
         """enqueue() + wait; returns the counts as a list of int."""
         torch = engine.require_cuda()
         out = self.enqueue(host_heads, n_keys, reduce)
         torch.cuda.current_stream(self.device).synchronize()
         return [int(v) for v in out.numpy().view(np.uint64)]
+
+
+def tally_live(redis_client, queue_names, match='processing-*', count=1000, chunk_keys=1 << 18,
+               chunk_bytes=16 << 20, device='cuda'):
+    """SCAN-count term of every queue from ONE scan of a live server, streamed.
+
+    The reference walks the keyspace once per queue and materialises every match in a Python
+    list (``len([x for x in scan])``, autoscaler.py:70-71).  Here the client's iterator
+    (``scan_iter``, the RedisClient seam, redis.py:163-202 of the reference) is drained once:
+    key bytes go straight into one of two pinned staging buffers (blob + offsets), and as soon
+    as a buffer is full it is copied to the GPU, cut to heads by ``kas_pack_heads`` and counted
+    by the match kernel while the scan fills the other buffer.  Nothing but the counts comes
+    back.  Names that are live globs (or too long for a record) are counted by the glob kernel
+    on the same chunks.  Returns a list of int in the order of ``queue_names``."""
+    torch = engine.require_cuda()
+    names = list(queue_names)
+    plain = [i for i, q in enumerate(names) if not _needs_glob_kernel(q)]
+    globs = [i for i, q in enumerate(names) if _needs_glob_kernel(q)]
+    dev = torch.device(device)
+    tables = []          # (indices, rec_bytes, device table, device counts)
+    todo = [plain[lo:lo + engine.MAX_PREFIXES] for lo in range(0, len(plain), engine.MAX_PREFIXES)]
+    while todo:
+        part = todo.pop()
+        part_names = [names[i] for i in part]
+        W = engine.rec_bytes_for(part_names)
+        try:
+            image = engine.build_prefix_table(part_names, W)
+        except engine.KasError as err:
+            if err.status != engine.KAS_ERR_UNSUPPORTED or len(part) < 2:
+                raise
+            todo += [part[:len(part) // 2], part[len(part) // 2:]]
+            continue
+        tables.append((part, W, torch.from_numpy(image).to(dev),
+                       torch.zeros(len(part), dtype=torch.int64, device=dev)))
+    patterns = [b'processing-' + _glob_escape(engine.encode_name(names[i])) + b':*' for i in globs]
+    glob_totals = [0] * len(globs)
+    max_w = max([t[1] for t in tables], default=16)
+
+    host_blob = [torch.empty(chunk_bytes + 16, dtype=torch.uint8).pin_memory() for _ in range(2)]
+    host_off = [torch.empty(chunk_keys + 1, dtype=torch.int64).pin_memory() for _ in range(2)]
+    views = [memoryview(t.numpy()) for t in host_blob]
+    d_blob = [torch.empty(chunk_bytes + 16, dtype=torch.uint8, device=dev) for _ in range(2)]
+    d_off = [torch.empty(chunk_keys + 1, dtype=torch.int64, device=dev) for _ in range(2)]
+    d_heads = torch.empty(chunk_keys * max_w, dtype=torch.uint8, device=dev)
+    done = [None, None]
+    stream = torch.cuda.current_stream(dev)
+    state = {'buf': 0, 'fill': 0, 'lens': [], 'chunks': 0, 'keys': 0}
+
+    def flush():
+        b, n = state['buf'], len(state['lens'])
+        if n == 0:
+            return
+        off = host_off[b].numpy()
+        off[0] = 0
+        np.cumsum(state['lens'], out=off[1:n + 1])
+        fill = state['fill']
+        d_blob[b][:fill].copy_(host_blob[b][:fill], non_blocking=True)
+        d_off[b][:n + 1].copy_(host_off[b][:n + 1], non_blocking=True)
+        for part, W, table, counts in tables:
+            engine.check(engine.lib().kas_pack_heads(engine.ptr(d_blob[b]), engine.ptr(d_off[b]), n, 0, W,
+                                                     engine.ptr(d_heads), engine.stream_ptr()), 'kas_pack_heads')
+            engine.match_count(d_heads, n, W, table, len(part), d_counts=counts, accumulate=True)
+        if patterns:
+            for lo in range(0, len(patterns), 256):
+                c = engine.glob_count(d_blob[b], d_off[b], n, patterns[lo:lo + 256])
+                for k, v in enumerate(engine.counts_to_host(c)):
+                    glob_totals[lo + k] += int(v)
+        ev = torch.cuda.Event()
+        ev.record(stream)
+        done[b] = ev
+        state['chunks'] += 1
+        state['keys'] += n
+        # fill the other buffer next; the scan may not overwrite it before its last use is over
+        state['buf'] = b ^ 1
+        state['fill'] = 0
+        state['lens'] = []
+        if done[b ^ 1] is not None:
+            done[b ^ 1].synchronize()
+
+    for key in redis_client.scan_iter(match=match, count=count):
+        kb = key if isinstance(key, (bytes, bytearray)) else str(key).encode('utf-8')
+        n = len(kb)
+        if n > chunk_bytes:
+            raise ValueError('a key of %d bytes does not fit the %d-byte staging buffer' % (n, chunk_bytes))
+        if state['fill'] + n > chunk_bytes or len(state['lens']) == chunk_keys:
+            flush()
+        a = state['fill']
+        views[state['buf']][a:a + n] = kb
+        state['fill'] = a + n
+        state['lens'].append(n)
+    flush()
+    out = [0] * len(names)
+    for part, W, table, counts in tables:
+        for i, c in zip(part, counts.cpu().numpy().view(np.uint64)):
+            out[i] = int(c)
+    for i, c in zip(globs, glob_totals):
+        out[i] = c
+    tally_live.last = {'chunks': state['chunks'], 'keys': state['keys']}
+    return out
 
 
 class SnapshotRedis(object):

@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIBDIR = os.path.join(HERE, 'lib')
 OUT = os.path.join(LIBDIR, 'libkas.so')
-SOURCES = ['kas_match.cu', 'kas_replay.cu', 'kas_events.cu', 'kas_glob.cu', 'kas_ingest.cu']
+SOURCES = ['kas_match.cu', 'kas_replay.cu', 'kas_events.cu', 'kas_glob.cu', 'kas_ingest.cu', 'kas_comm.cu']
 HEADERS = ['kas_common.cuh', 'kas_table.h', 'kas_decide.cuh', os.path.join('..', '..', 'include', 'kas.h')]
 NVCC = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
 FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
@@ -43,7 +43,7 @@ def build(force=False, verbose=False):
             sys.stderr.write(r.stdout + r.stderr)
             raise RuntimeError('nvcc failed on %s' % s)
         objs.append(o)
-    cmd = [NVCC, '-shared', '-gencode', 'arch=compute_100a,code=sm_100a', '-o', OUT] + objs
+    cmd = [NVCC, '-shared', '-gencode', 'arch=compute_100a,code=sm_100a', '-o', OUT] + objs + ['-ldl']
     subprocess.check_call(cmd)
     with open(os.path.join(LIBDIR, 'ptxas.log'), 'w') as f:
         f.write('\n'.join(log))

@@ -7,6 +7,7 @@
 namespace kas {
 
 void set_cuda_error(cudaError_t e, const char *where);
+void set_text_error(const char *where, const char *what);   // same slot, for non-CUDA libraries (NCCL)
 
 #define KAS_CUDA_TRY(expr)                                    \
     do {                                                      \

@@ -87,6 +87,87 @@ events_kernel(const __grid_constant__ EventParams P) {
     }
 }
 
+// ---- time to the first pod after a burst ------------------------------------
+// The same recurrence once more, keeping per resource what a cost report needs beside
+// pod-hours and churn: how long work that arrives at an idle resource waits for its first
+// pod (definition in include/kas.h).  One thread per
+// resource; sums[0..4] = served, unserved, wait_sum, max wait, pending over all resources.
+template <typename E, int MODE>
+__global__ void __launch_bounds__(kEventThreads)
+first_pod_kernel(const __grid_constant__ EventParams P, kas_first_pod *__restrict__ out,
+                 unsigned long long *__restrict__ sums) {
+    const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = r < P.R;
+    uint32_t served = 0, unserved = 0, wmax = 0, pending = 0;
+    unsigned long long wsum = 0;
+    if (valid) {
+        const PolDev pol = P.pol;
+        const uint64_t q0 = P.group_off ? P.group_off[r] : r;
+        const uint64_t q1 = P.group_off ? P.group_off[r + 1] : r + 1;
+        int32_t cur = P.cur0 ? P.cur0[r] : 0;     // what the controller reads
+        int32_t spec = cur;
+        const uint32_t D = P.startup_delay;
+        SpecWindow win;
+        win.init(spec, D);
+        long long prev_tally = 0;
+        int64_t waiting = -1;
+        for (uint32_t t = 0; t < P.T; ++t) {
+            const E *lrow = static_cast<const E *>(P.llen) + (uint64_t)t * P.Q;
+            const E *irow = static_cast<const E *>(P.inprog) + (uint64_t)t * P.Q;
+            const int32_t *iq = static_cast<const int32_t *>(P.inprog);
+            long long sum = 0, total = 0;
+            for (uint64_t q = q0; q < q1; ++q) {
+                const int32_t l = ld_trace<E>(lrow + q);
+                const int32_t ip = P.inprog_mode == 2 ? ld_trace<E>(irow + q)
+                                                      : (P.inprog_mode == 1 ? __ldg(iq + q) : 0);
+                total += (long long)l + (long long)ip;                    // autoscaler.py:73
+                sum += decide<MODE>(l, ip, pol, cur);                     // :255-257
+            }
+            const int32_t read = cur;                                     // :252
+            const int32_t want = clip64(sum, pol.mn, pol.mx, cur);        // :259
+            if (want != cur && !(P.patch_fail && P.patch_fail[(uint64_t)t * P.R + r])) spec = want;
+            cur = D ? win.push(spec, t, D) : spec;                        // running after the tick
+            if (waiting < 0 && total > 0 && prev_tally <= 0 && read <= 0) waiting = t;
+            if (waiting >= 0) {
+                if (cur > 0) {
+                    const uint32_t w = (uint32_t)(t - waiting);
+                    ++served; wsum += w; wmax = max(wmax, w);
+                    waiting = -1;
+                } else if (total <= 0) {
+                    ++unserved;
+                    waiting = -1;
+                }
+            }
+            prev_tally = total;
+        }
+        if (waiting >= 0) pending = (uint32_t)(P.T - waiting);
+        if (out) {
+            kas_first_pod o;
+            o.n_served = served; o.n_unserved = unserved; o.wait_max = wmax; o.pending = pending;
+            o.wait_sum = wsum;
+            out[r] = o;
+        }
+    }
+    if (sums) {
+        unsigned long long a = served, b = unserved, c = wsum, d = wmax, e = pending;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            a += __shfl_xor_sync(0xFFFFFFFFu, a, o);
+            b += __shfl_xor_sync(0xFFFFFFFFu, b, o);
+            c += __shfl_xor_sync(0xFFFFFFFFu, c, o);
+            d = max(d, __shfl_xor_sync(0xFFFFFFFFu, d, o));
+            e += __shfl_xor_sync(0xFFFFFFFFu, e, o);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(sums + 0, a);
+            atomicAdd(sums + 1, b);
+            atomicAdd(sums + 2, c);
+            atomicMax(sums + 3, d);
+            atomicAdd(sums + 4, e);
+        }
+    }
+}
+
 // ---- exclusive scan of the counts, in place over event_off[1..R] -------------
 // (event_off[i+1] becomes the sum of counts 0..i, i.e. the end of resource i.)
 __global__ void __launch_bounds__(kScanThreads)
@@ -323,6 +404,29 @@ int kas_patch_event_emit(const kas_replay_args *args, uint32_t policy_index, con
     P.capacity = capacity;
     if (capacity == 0) return KAS_OK;
     return launch_events<true>(P, mode, static_cast<cudaStream_t>(stream));
+}
+
+int kas_first_pod_latency(const kas_replay_args *args, uint32_t policy_index, kas_first_pod *d_out,
+                          int64_t *d_sums, void *stream_v) {
+    if (!args || (!d_out && !d_sums)) return KAS_ERR_INVALID;
+    if (!aligned(d_out, 8) || !aligned(d_sums, 8)) return KAS_ERR_ALIGNMENT;
+    EventParams P;
+    int mode = 0;
+    const int st = fill_event_params(args, policy_index, P, mode);
+    if (st != KAS_OK) return st;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+    unsigned long long *sums = reinterpret_cast<unsigned long long *>(d_sums);
+    if (sums) KAS_CUDA_TRY(cudaMemsetAsync(sums, 0, 5 * sizeof(unsigned long long), stream));
+    const unsigned grid = (unsigned)((P.R + kEventThreads - 1) / kEventThreads);
+    if (P.u16) {
+        if (mode == kGeneric) first_pod_kernel<uint16_t, kGeneric><<<grid, kEventThreads, 0, stream>>>(P, d_out, sums);
+        else first_pod_kernel<uint16_t, kSimple><<<grid, kEventThreads, 0, stream>>>(P, d_out, sums);
+    } else {
+        if (mode == kGeneric) first_pod_kernel<int32_t, kGeneric><<<grid, kEventThreads, 0, stream>>>(P, d_out, sums);
+        else first_pod_kernel<int32_t, kSimple><<<grid, kEventThreads, 0, stream>>>(P, d_out, sums);
+    }
+    KAS_CUDA_TRY(cudaGetLastError());
+    return KAS_OK;
 }
 
 int kas_patch_event_offsets_static(const kas_replay_args *args, uint32_t policy_index,

@@ -22,6 +22,10 @@ void set_cuda_error(cudaError_t e, const char *where) {
              cudaGetErrorString(e));
 }
 
+void set_text_error(const char *where, const char *what) {
+    snprintf(g_cuda_error, sizeof(g_cuda_error), "%s: %s", where, what);
+}
+
 int sm_count() {
     static thread_local int cached_dev = -1;
     static thread_local int cached_sms = 0;

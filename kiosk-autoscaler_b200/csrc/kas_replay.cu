@@ -1255,8 +1255,17 @@ replay_grouped_tiled_kernel(const __grid_constant__ ReplayParams P) {
 #ifndef KAS_GS_STAGE_KB
 #define KAS_GS_STAGE_KB 12
 #endif
-constexpr int kGsThreads = 128;
-constexpr int kGsStages = 3;
+#ifndef KAS_GS_THREADS
+#define KAS_GS_THREADS 128
+#endif
+constexpr int kGsThreads = KAS_GS_THREADS;     // resources per block; a power of two
+#ifndef KAS_GS_UNROLL_SP4
+#define KAS_GS_UNROLL_SP4 0    /* unroll the queue loop under four policies per thread as well */
+#endif
+#ifndef KAS_GS_STAGES
+#define KAS_GS_STAGES 3
+#endif
+constexpr int kGsStages = KAS_GS_STAGES;       // tile buffers; kGsStages - 1 tiles are in flight
 constexpr uint32_t kGsStageBytes = KAS_GS_STAGE_KB * 1024;   // per stage and array
 constexpr uint32_t kGsMaxTileTicks = 32;
 constexpr uint32_t kGsMaxOwn = 2048;          // queues of one resource: x kGsMaxPods stays below 2^31
@@ -1323,8 +1332,8 @@ replay_grouped_sorted_kernel(const __grid_constant__ ReplayParams P) {
     __syncthreads();
     if (tid < nres) {
         const uint32_t p = s_cnt[key] + pos;
-        const uint32_t rot = (bx * 2654435761u) >> 30;                   // 0..3
-        s_perm[((((p >> 5) + rot) & 3u) << 5) | (p & 31u)] = (uint16_t)tid;
+        const uint32_t rot = (bx * 2654435761u) >> 27;                   // a pseudo-random turn of the warps
+        s_perm[((((p >> 5) + rot) & (kGsThreads / 32 - 1)) << 5) | (p & 31u)] = (uint16_t)tid;
     }
     // the per-queue in-progress counts of the run, once (IPMODE 1)
     int32_t *s_ipq = reinterpret_cast<int32_t *>(gsm + kGsStages * kArrays * kStageVec);
@@ -1360,8 +1369,6 @@ replay_grouped_sorted_kernel(const __grid_constant__ ReplayParams P) {
     uint32_t np[SP];
 #pragma unroll
     for (int s = 0; s < SP; ++s) { cur[s] = 0; pt[s] = 0; np[s] = 0u; }
-    const uint32_t one = (uint32_t)P.one;
-
     if (tiled) {
         const uint32_t row_vec = (uint32_t)row_vec64;
         const uint32_t row_elems = row_vec * kEPP;
@@ -1370,20 +1377,23 @@ replay_grouped_sorted_kernel(const __grid_constant__ ReplayParams P) {
         const uint32_t n_tiles = (T + tile_ticks - 1) / tile_ticks;
         const uint32_t n_own = (uint32_t)(q1 - q0);
         const uint32_t j0 = valid ? (uint32_t)(q0 - a0) : 0u;             // place inside the staged run
-        // all lanes of the warp own groups of one size: the loop over queues is unrolled for it
-        const uint32_t n_first = __shfl_sync(0xFFFFFFFFu, n_own, 0);
-        const bool uniform = __all_sync(0xFFFFFFFFu, valid && n_own == n_first);
+        // the lanes of a warp own groups of (nearly) one size: the loop over queues is unrolled for
+        // the largest of them, lanes with fewer queues sit out the last rounds under a predicate
+        const uint32_t n_max = __reduce_max_sync(0xFFFFFFFFu, valid ? n_own : 0u);
+        // one bulk copy per tick row, issued by the lanes of warp 0 side by side (a single thread
+        // issuing them one after another holds its warp, and with it the block's barrier, back)
         auto stage = [&](uint32_t k) {
-            if (tid == 0 && k < n_tiles) {
+            if (tid < 32 && k < n_tiles) {
                 const uint32_t t0 = k * tile_ticks;
                 const uint32_t nt = min(tile_ticks, T - t0);
                 uint64_t *bar = &bars[k % kGsStages];
                 int4 *dl = gsm + (k % kGsStages) * kArrays * kStageVec;
                 int4 *di = dl + kStageVec;
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // earlier reads of this buffer are done
-                mbar_expect_tx(bar, nt * row_bytes * kArrays);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // earlier reads of this buffer are done
+                if (tid == 0) mbar_expect_tx(bar, nt * row_bytes * kArrays);
+                __syncwarp();
                 if (row_bytes) {
-                    for (uint32_t t = 0; t < nt; ++t) {
+                    for (uint32_t t = tid; t < nt; t += 32) {
                         const uint64_t g = (uint64_t)(t0 + t) * Q + a0;
                         bulk_copy_g2s(dl + t * row_vec, static_cast<const E *>(P.llen) + g, row_bytes, bar);
                         if (IPMODE == 2) bulk_copy_g2s(di + t * row_vec, static_cast<const E *>(P.inprog) + g, row_bytes, bar);
@@ -1391,12 +1401,12 @@ replay_grouped_sorted_kernel(const __grid_constant__ ReplayParams P) {
                 }
             }
         };
-        stage(0);
-        stage(1);
+#pragma unroll
+        for (int i = 0; i < kGsStages - 1; ++i) stage((uint32_t)i);
         for (uint32_t k = 0; k < n_tiles; ++k) {
             mbar_wait(&bars[k % kGsStages], (k / kGsStages) & 1u);       // tile k has landed
             __syncthreads();                                              // all are done with tile k-1
-            stage(k + 2);                                                 // refill the buffer tile k-1 occupied
+            stage(k + kGsStages - 1);                                     // refill the buffer tile k-1 occupied
             if (!valid) continue;
             const uint32_t t0 = k * tile_ticks;
             const uint32_t nt = min(tile_ticks, T - t0);
@@ -1426,7 +1436,9 @@ replay_grouped_sorted_kernel(const __grid_constant__ ReplayParams P) {
 #pragma unroll
                     for (int s = 0; s < SP; ++s) sum[s] = 0u;
                     uint32_t any = 0u;
-                    auto one_queue = [&](uint32_t j) {
+                    // `live_q`: the queue is this resource's own (a lane with fewer queues than the
+                    // warp's largest group reads on into its neighbour's and adds nothing)
+                    auto one_queue = [&](uint32_t j, bool live_q) {
                         uint32_t tally = (uint32_t)lrow[j];
                         if constexpr (kCheck) any |= tally;
                         if constexpr (IPMODE == 1) tally += (uint32_t)iq[j];          // range-checked when staged
@@ -1438,14 +1450,16 @@ replay_grouped_sorted_kernel(const __grid_constant__ ReplayParams P) {
 #pragma unroll
                         for (int s = 0; s < SP; ++s) {
                             const uint32_t q = K1 ? tally : quotient_small(tally + 1u, pol[s]);
-                            sum[s] += (uint32_t)finish_simple3(q, keep_factor(q, keep[s], one), pol[s], cur[s]);   // :255-257
+                            const uint32_t v = (uint32_t)finish_simple3(q, __viaddmin_u32(q, keep[s].add, keep[s].lim),
+                                                                        pol[s], cur[s]);                     // :255-257
+                            if (live_q) sum[s] += v;
                         }
                     };
                     if constexpr (N > 0) {
 #pragma unroll
-                        for (int j = 0; j < N; ++j) one_queue((uint32_t)j);
+                        for (int j = 0; j < N; ++j) one_queue((uint32_t)j, (uint32_t)j < n_own);
                     } else {
-                        for (uint32_t j = 0; j < n_own; ++j) one_queue(j);
+                        for (uint32_t j = 0; j < n_own; ++j) one_queue(j, true);
                     }
                     int32_t want[SP];
                     if (kCheck && any >= kSmallTallyTerm) {
@@ -1453,7 +1467,7 @@ replay_grouped_sorted_kernel(const __grid_constant__ ReplayParams P) {
                     } else {
 #pragma unroll
                         for (int s = 0; s < SP; ++s)                                                        // :259
-                            want[s] = finish_simple3(sum[s], keep_factor(sum[s], keep[s], one), pol[s], cur[s]);
+                            want[s] = finish_simple3(sum[s], __viaddmin_u32(sum[s], keep[s].add, keep[s].lim), pol[s], cur[s]);
                     }
 #pragma unroll
                     for (int s = 0; s < SP; ++s) {
@@ -1463,8 +1477,8 @@ replay_grouped_sorted_kernel(const __grid_constant__ ReplayParams P) {
                     }
                 }
             };
-            if (SP == 1 && uniform) {
-                switch (n_first) {
+            if (SP == 1 || KAS_GS_UNROLL_SP4) {
+                switch (n_max) {
                     case 1: run_tile(std::integral_constant<int, 1>{}); break;
                     case 2: run_tile(std::integral_constant<int, 2>{}); break;
                     case 3: run_tile(std::integral_constant<int, 3>{}); break;
@@ -1619,14 +1633,16 @@ static int launch_grouped(const ReplayParams &P, int mode, cudaStream_t stream) 
 #endif
     if (lean) {
         const bool k1 = SP == 1 && P.pol[0].k1 != 0u;
+        const unsigned gs_grid = (unsigned)(((P.R + kGsThreads - 1) / kGsThreads) * ny);
+        // (+ 64 bytes: a lane may read up to seven elements past the last staged row)
         const size_t smem = (size_t)kGsStages * (tickip ? 2 : 1) * kGsStageBytes +
-                            (P.inprog_mode == 1 ? (size_t)kGsStageBytes / sizeof(E) * 4 : 0);
+                            (P.inprog_mode == 1 ? (size_t)kGsStageBytes / sizeof(E) * 4 : 0) + 64;
 #define KAS_LAUNCH_GS(IPM, KONE)                                                                   \
     do {                                                                                           \
         auto kern = replay_grouped_sorted_kernel<E, SP, IPM, KONE>;                                \
         KAS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
                                           (int)smem));                                             \
-        kern<<<grid, kGsThreads, smem, stream>>>(P);                                               \
+        kern<<<gs_grid, kGsThreads, smem, stream>>>(P);                                            \
     } while (0)
         if constexpr (SP == 1) {
             if (k1) {

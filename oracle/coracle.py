@@ -41,6 +41,10 @@ def lib():
         L.kas_oracle_replay.restype = None
         L.kas_oracle_replay_delay.argtypes = L.kas_oracle_replay.argtypes[:-1] + [C.c_uint32, C.c_int]
         L.kas_oracle_replay_delay.restype = None
+        L.kas_oracle_first_pod.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_uint32, C.c_uint64, C.c_void_p,
+                                           C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                           C.c_uint32, C.c_int]
+        L.kas_oracle_first_pod.restype = None
         L.kas_oracle_trace_value.argtypes = [C.c_uint64, C.c_uint64, C.c_uint32]
         L.kas_oracle_trace_value.restype = C.c_int32
         L.kas_oracle_trace_fill.argtypes = [C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint64,
@@ -148,6 +152,36 @@ def replay(llen, inprog, group_off, cur0, policies, want_dense=False, threads=No
     if want_dense:
         out['dense'] = dense
     return out
+
+
+FIRST_POD_FIELDS = ('n_served', 'n_unserved', 'wait_sum', 'wait_max', 'pending')
+
+
+def first_pod(llen, inprog, group_off, cur0, policy, threads=None, patch_fail=None, startup_delay=0):
+    """Time to the first pod after a burst per resource (oracle.first_pod_latency over a fleet):
+    dict of int64 arrays [R] keyed by FIRST_POD_FIELDS."""
+    llen = np.ascontiguousarray(llen, dtype=np.int32)
+    T, Q = llen.shape
+    mode, ip = 0, None
+    if inprog is not None:
+        ip = np.ascontiguousarray(inprog, dtype=np.int32)
+        mode = 1 if ip.ndim == 1 else 2
+    go, R = None, Q
+    if group_off is not None:
+        go = np.ascontiguousarray(group_off, dtype=np.uint64)
+        R = len(go) - 1
+    c0 = None if cur0 is None else np.ascontiguousarray(cur0, dtype=np.int32)
+    pol = np.ascontiguousarray(policy, dtype=np.int32).reshape(3)
+    if pol[0] == 0:
+        raise ZeroDivisionError('integer division or modulo by zero')
+    out = np.zeros((R, 5), dtype=np.int64)
+    pf = None if patch_fail is None else np.ascontiguousarray(patch_fail, dtype=np.uint8).reshape(T, R)
+    lib().kas_oracle_first_pod(llen.ctypes.data, None if ip is None else ip.ctypes.data, mode, T, Q,
+                               None if go is None else go.ctypes.data, R,
+                               None if c0 is None else c0.ctypes.data, pol.ctypes.data, out.ctypes.data,
+                               None if pf is None else pf.ctypes.data, int(startup_delay),
+                               threads or max_threads())
+    return {k: out[:, i].copy() for i, k in enumerate(FIRST_POD_FIELDS)}
 
 
 def trace_fill(seed, T, q_first, n_q, threads=None):

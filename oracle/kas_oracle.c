@@ -239,6 +239,64 @@ KAS_EXPORT void kas_oracle_replay_delay(const int32_t *llen, const int32_t *inpr
     }
 }
 
+/* ---- Time to the first pod after a burst (report on top of the replay) -----
+ * Same loop as kas_oracle_replay_delay for ONE policy, with the bookkeeping of
+ * oracle.first_pod_latency (see there for the definition).  out [R][5] int64:
+ * n_served, n_unserved, wait_sum, wait_max, pending.                         */
+KAS_EXPORT void kas_oracle_first_pod(const int32_t *llen, const int32_t *inprog, int inprog_mode,
+                                     uint32_t T, uint64_t Q,
+                                     const uint64_t *group_off, uint64_t R,
+                                     const int32_t *cur0, const int32_t *policy /* kpp, min, max */,
+                                     int64_t *out, const uint8_t *patch_fail /* [T][R] or NULL */,
+                                     uint32_t startup_delay, int threads)
+{
+    if (startup_delay > KAS_ORACLE_MAX_DELAY) startup_delay = KAS_ORACLE_MAX_DELAY;
+    const int64_t kpp = policy[0], mn = policy[1], mx = policy[2];
+#pragma omp parallel for schedule(static) num_threads(threads > 0 ? threads : 1)
+    for (uint64_t r = 0; r < R; ++r) {
+        uint64_t q0 = group_off ? group_off[r] : r;
+        uint64_t q1 = group_off ? group_off[r + 1] : r + 1;
+        int64_t spec = cur0 ? cur0[r] : 0, avail = spec;
+        int64_t hist[KAS_ORACLE_MAX_DELAY];
+        for (uint32_t i = 0; i < startup_delay; ++i) hist[i] = spec;
+        int64_t waiting = -1, prev_tally = 0;
+        int64_t served = 0, unserved = 0, wsum = 0, wmax = 0;
+        for (uint32_t t = 0; t < T; ++t) {
+            int64_t cur = avail, sum = 0, total = 0;
+            for (uint64_t q = q0; q < q1; ++q) {
+                int64_t tally = llen[(uint64_t)t * Q + q];
+                if (inprog_mode == 1) tally += inprog[q];
+                else if (inprog_mode == 2) tally += inprog[(uint64_t)t * Q + q];
+                total += tally;
+                sum += clip64(floordiv64(tally, kpp), mn, mx, cur);
+            }
+            int64_t desired = clip64(sum, mn, mx, cur);
+            if (desired != cur && !(patch_fail && patch_fail[(uint64_t)t * R + r])) spec = desired;
+            avail = spec;
+            for (uint32_t i = 0; i < startup_delay; ++i)
+                if (hist[i] < avail) avail = hist[i];
+            if (startup_delay) hist[t % startup_delay] = spec;
+            if (waiting < 0 && total > 0 && prev_tally <= 0 && cur <= 0) waiting = t;
+            if (waiting >= 0) {
+                if (avail > 0) {
+                    int64_t w = (int64_t)t - waiting;
+                    served += 1; wsum += w; if (w > wmax) wmax = w;
+                    waiting = -1;
+                } else if (total <= 0) {
+                    unserved += 1;
+                    waiting = -1;
+                }
+            }
+            prev_tally = total;
+        }
+        out[5 * r + 0] = served;
+        out[5 * r + 1] = unserved;
+        out[5 * r + 2] = wsum;
+        out[5 * r + 3] = wmax;
+        out[5 * r + 4] = waiting >= 0 ? (int64_t)T - waiting : 0;
+    }
+}
+
 KAS_EXPORT void kas_oracle_replay(const int32_t *llen, const int32_t *inprog, int inprog_mode,
                                   uint32_t T, uint64_t Q,
                                   const uint64_t *group_off, uint64_t R,

@@ -364,6 +364,80 @@ def only_running_cases():
     return cases
 
 
+def _first_pod_stats(tally, seen, running):
+    """The written definition (include/kas.h, kas_first_pod_latency) applied to what the
+    reference did: tally[t] = sum of redis_keys after tally_queues, seen[t] = what scale() read
+    through get_current_pods on tick t, running[t] = what the same call returns after tick t."""
+    out = dict(n_served=0, n_unserved=0, wait_sum=0, wait_max=0, pending=0)
+    waiting, prev = -1, 0
+    for t in range(len(tally)):
+        if waiting < 0 and tally[t] > 0 and prev <= 0 and seen[t] <= 0:
+            waiting = t
+        if waiting >= 0:
+            if running[t] > 0:
+                w = t - waiting
+                out['n_served'] += 1
+                out['wait_sum'] += w
+                out['wait_max'] = max(out['wait_max'], w)
+                waiting = -1
+            elif tally[t] <= 0:
+                out['n_unserved'] += 1
+                waiting = -1
+        prev = tally[t]
+    if waiting >= 0:
+        out['pending'] = len(tally) - waiting
+    return out
+
+
+def _run_first_pod(queues, depths, kpp, mn, mx, cur0, rtype, delay, fails=None):
+    """scale() of the reference over a trace, reading pods through its own get_current_pods
+    (only_running=True when a start-up delay is modelled, autoscaler.py:176-177), with the reads
+    before and after every tick and the tally it computed recorded."""
+    names = queues.split(',')
+    redis = refload.StubRedis()
+    kube = refload.StatefulKube('r', rtype, cur0, startup_delay=delay)
+    s = refload.make_reference_scaler(redis, queues, ',', kube, only_running=delay > 0)
+    seen, running, tally = [], [], []
+    for t, row in enumerate(depths):
+        redis.lists = dict(zip(names, row))
+        kube.fail_next_patch = bool(fails and fails[t])
+        seen.append(s.get_current_pods('ns', rtype, 'r'))
+        s.scale('ns', rtype, 'r', min_pods=mn, max_pods=mx, keys_per_pod=kpp)
+        kube.end_tick()
+        running.append(s.get_current_pods('ns', rtype, 'r'))
+        tally.append(sum(s.redis_keys.values()))
+    return dict(queues=queues, depths=depths, kpp=kpp, min=mn, max=mx, cur0=cur0, type=rtype,
+                delay=delay if rtype == 'deployment' else 0, fails=fails, seen=seen, running=running,
+                stats=_first_pod_stats(tally, seen, running))
+
+
+def first_pod_cases():
+    import random
+    rnd = random.Random(20261108)
+    cases = []
+    bursts = [[0], [0], [3], [6], [0], [0], [1], [1], [9], [0], [2], [0], [0], [0], [7], [7]]
+    for delay in (0, 1, 3):
+        cases.append(_run_first_pod('q', bursts, 1, 0, 8, 0, 'deployment', delay))
+        cases.append(_run_first_pod('q', bursts, 4, 0, 8, 0, 'deployment', delay))    # small bursts stay below one pod
+        cases.append(_run_first_pod('q', bursts, 1, 1, 4, 0, 'deployment', delay))    # min_pods keeps one up
+        cases.append(_run_first_pod('q', bursts, 2, 0, 8, 0, 'job', delay))
+    for _ in range(70):
+        nq = rnd.choice([1, 1, 2, 3])
+        T = rnd.randint(8, 60)
+        depths, level = [], 0
+        for t in range(T):
+            if rnd.random() < 0.3:
+                level = rnd.choice([0, 0, 0, 1, 2, 5, 12])
+            depths.append([max(0, level + rnd.randint(-1, 1)) if level else 0 for _ in range(nq)])
+        fails = [rnd.random() < 0.2 for _ in range(T)] if rnd.random() < 0.3 else None
+        cases.append(_run_first_pod(','.join('q%d' % i for i in range(nq)), depths,
+                                    rnd.choice([1, 2, 3, 6]), rnd.choice([0, 0, 0, 1]),
+                                    rnd.choice([1, 4, 16]), rnd.choice([0, 0, 0, 3]),
+                                    rnd.choice(['deployment', 'deployment', 'job']),
+                                    rnd.choice([0, 0, 1, 2, 4]), fails))
+    return cases
+
+
 def main():
     assert refload.available(), 'needs /root/reference'
     import logging
@@ -372,7 +446,8 @@ def main():
     only = set(sys.argv[1:])          # fixture names to (re)write; none given: all of them
     for name, fn in [('known_answers', known_answers), ('decisions', decisions),
                      ('scale_cases', scale_cases), ('tally_cases', tally_cases),
-                     ('only_running_cases', only_running_cases)]:
+                     ('only_running_cases', only_running_cases),
+                     ('first_pod_cases', first_pod_cases)]:
         if only and name not in only:
             continue
         with open(os.path.join(GOLD, name + '.json'), 'w') as f:

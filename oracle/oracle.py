@@ -243,6 +243,64 @@ def replay_resource(llen_rows: Sequence[Sequence[int]],
     return after, patches
 
 
+def first_pod_latency(llen_rows: Sequence[Sequence[int]],
+                      inprog_rows: Optional[Sequence[Sequence[int]]],
+                      keys_per_pod: int, min_pods: int, max_pods: int,
+                      cur0: int = 0,
+                      patch_fails: Optional[Sequence[bool]] = None,
+                      startup_delay: int = 0) -> dict:
+    """Time to the first pod after a burst, for one resource under one policy (a report on
+    top of the replayed ``scale`` loop, autoscaler.py:244-273; the reference itself never
+    computes it -- README.md:7 states the purpose it serves, "minimizing GPU costs").
+
+    A burst starts on a tick whose tally (sum over the resource's queues of LLEN + SCAN count,
+    autoscaler.py:73) is positive after a tick where it was not (before the first tick it counts
+    as 0), while the controller reads 0 pods on that tick (autoscaler.py:252; the AVAILABLE
+    pods under ``startup_delay``, autoscaler.py:176-177) and no earlier burst is still waiting.
+    It is SERVED on the first tick at or after its start after which pods are running (what the
+    next tick will read is positive); its wait is that tick minus the starting tick (0 when the
+    same tick's patch brings pods up).  If the tally returns to 0 first, the burst went UNSERVED.
+    Returns n_served, n_unserved, wait_sum, wait_max and pending (ticks the last burst has
+    waited when the trace ends, 0 if none is waiting)."""
+    spec = cur0
+    avail = cur0
+    hist = [cur0] * startup_delay
+    waiting = -1
+    prev_tally = 0
+    out = dict(n_served=0, n_unserved=0, wait_sum=0, wait_max=0, pending=0)
+    T = 0
+    for t, row in enumerate(llen_rows):
+        T = t + 1
+        if inprog_rows is None:
+            tallies = list(row)
+        else:
+            tallies = [a + b for a, b in zip(row, inprog_rows[t])]
+        tally = sum(tallies)
+        cur = avail
+        desired = scale_step(tallies, keys_per_pod, min_pods, max_pods, cur)
+        if desired != cur and not (patch_fails is not None and patch_fails[t]):
+            spec = desired
+        avail = min([spec] + hist)
+        if startup_delay:
+            hist[t % startup_delay] = spec
+        if waiting < 0 and tally > 0 and prev_tally <= 0 and cur <= 0:
+            waiting = t
+        if waiting >= 0:
+            if avail > 0:
+                w = t - waiting
+                out['n_served'] += 1
+                out['wait_sum'] += w
+                out['wait_max'] = max(out['wait_max'], w)
+                waiting = -1
+            elif tally <= 0:
+                out['n_unserved'] += 1
+                waiting = -1
+        prev_tally = tally
+    if waiting >= 0:
+        out['pending'] = T - waiting
+    return out
+
+
 def replay_totals(after: Sequence[int], cur0: int) -> Tuple[int, int, int]:
     """Reductions the replay kernel reports per (resource, policy):
     pod_ticks = sum of replicas after each tick, n_patches = number of ticks on

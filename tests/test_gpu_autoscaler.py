@@ -77,3 +77,33 @@ def test_scale_does_not_raise_and_swallows_api_exception():
     scaler.scale_resource = bad_scale_resource
     for resource_type in scaler.managed_resource_types:
         scaler.scale(namespace='namespace', resource_type=resource_type, name='test')
+
+
+def test_live_scan_is_streamed_in_chunks():
+    """tally_live: one pass over the client's scan_iter, keys staged in pinned chunks and counted
+    chunk by chunk on the GPU (prefix kernel for literal names, glob kernel for live globs),
+    against the oracle's per-queue scans of the same keyspace."""
+    import autoscaler
+    from autoscaler import engine, snapshot
+    from oracle import coracle
+    names = helpers.c2_queue_names(24) + ['pre*', 'tr[a-c]ck', 'x' * 60]
+    _, blob, off = engine.synth_keys_host(31, 0, 30_000, helpers.c2_queue_names(24), long_tail=True,
+                                          want_heads=False, want_blob=True)
+    keys = [bytes(blob[off[i]:off[i + 1]]) for i in range(30_000)]
+    keys += [b'processing-' + b'x' * 60 + b':1', b'processing-trbck:9']
+    client = helpers.ListRedis(keyspace=keys)
+    got = snapshot.tally_live(client, names, chunk_keys=4096, chunk_bytes=200_000)
+    assert snapshot.tally_live.last['chunks'] >= 4 and snapshot.tally_live.last['keys'] == len(
+        [k for k in keys if k.startswith(b'processing-')])
+    live = [k for k in keys if k.startswith(b'processing-')]
+    want = [sum(coracle.glob_match(b'processing-' + engine.encode_name(q) + b':*', k) for k in live) for q in names]
+    assert got == want and sum(got[-3:]) > 0
+    assert client.scans == ['processing-*']                      # ONE scan, not one per queue
+    # str keys (decode_responses=True, as the reference's client is configured)
+    client2 = helpers.ListRedis(keyspace=keys)
+    client2.scan_iter = lambda match=None, count=None: (k.decode('latin-1') for k in live[:500])
+    want2 = [sum(coracle.glob_match(b'processing-' + engine.encode_name(q) + b':*', k.decode('latin-1').encode('utf-8'))
+                 for k in live[:500]) for q in names]
+    assert snapshot.tally_live(client2, names) == want2
+    with pytest.raises(ValueError):
+        snapshot.tally_live(helpers.ListRedis(keyspace=[b'processing-' + b'y' * 300]), ['a'], chunk_bytes=128)

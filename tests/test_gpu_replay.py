@@ -562,3 +562,62 @@ def test_grouped_offsets_that_overlap_or_go_back():
     assert (tot['pod_ticks'] == want['pod_ticks']).all()
     assert (tot['n_patches'] == want['n_patches']).all()
     assert (tot['final_current'] == want['final']).all()
+
+
+def test_first_pod_latency_reference_fixture():
+    """f4: time to the first pod after a burst, against what the reference's own scale() loop
+    did (tests/golden/first_pod_cases.json)."""
+    import autoscaler
+    for c in helpers.golden_json('first_pod_cases'):
+        depths = np.array(c['depths'], dtype=np.int32)
+        nq = depths.shape[1]
+        fails = None if c['fails'] is None else np.array(c['fails']).reshape(-1, 1)
+        got = autoscaler.replay.first_pod_latency(
+            depths, [(c['kpp'], c['min'], c['max'])], group_off=np.array([0, nq], dtype=np.uint64),
+            cur0=np.array([c['cur0']]), resource_type=c['type'], patch_fail=fails,
+            startup_delay=c['delay'], want_rows=True)[0]
+        row = got['rows'][0]
+        assert {k: int(row[k]) for k in ('n_served', 'n_unserved', 'wait_sum', 'wait_max', 'pending')} == c['stats']
+        assert got['n_served'] == c['stats']['n_served'] and got['wait_max'] == c['stats']['wait_max']
+
+
+@pytest.mark.parametrize('shape', ['identity', 'grouped', 'identity_u16'])
+@pytest.mark.parametrize('delay', [0, 2, 16])
+@pytest.mark.parametrize('ipmode', [0, 1, 2])
+def test_first_pod_latency_fleets_vs_oracle(shape, delay, ipmode):
+    import autoscaler
+    from oracle import coracle
+    rng = np.random.default_rng(stable_seed('ttfp', shape, delay, ipmode))
+    T, Q = 120, 5000
+    llen, go = helpers.random_fleet(rng, T, Q, grouped=(shape == 'grouped'), neg=(shape == 'grouped'))
+    llen[:, rng.random(Q) < 0.5] //= 8                     # quiet queues: bursts that need several ticks
+    R = Q if go is None else len(go) - 1
+    cur0 = rng.integers(0, 3, size=R).astype(np.int32) * (rng.random(R) < 0.3)
+    fail = rng.random((T, R)) < 0.1
+    np_t = np.uint16 if shape == 'identity_u16' else np.int32
+    inprog = ip_dev = None
+    if ipmode == 1:
+        inprog = (rng.integers(0, 3, size=Q) * (rng.random(Q) < 0.2)).astype(np.int32)
+        ip_dev = inprog
+    elif ipmode == 2:
+        inprog = (rng.integers(0, 4, size=(T, Q)) * (rng.random((T, Q)) < 0.1)).astype(np.int32)
+        ip_dev = inprog.astype(np_t)
+    pols = [(1, 0, 1), (6, 0, 8), (3, 1, 4), (-2, 0, 5), (40, 0, 2)]
+    got = autoscaler.replay.first_pod_latency(llen.astype(np_t), pols, inprog=ip_dev, group_off=go,
+                                              cur0=cur0.astype(np.int32), patch_fail=fail, startup_delay=delay,
+                                              want_rows=True)
+    seen_wait = 0
+    for pol, g in zip(pols, got):
+        want = coracle.first_pod(llen, inprog, go, cur0.astype(np.int32), pol, patch_fail=fail, startup_delay=delay)
+        for k in ('n_served', 'n_unserved', 'wait_sum', 'wait_max', 'pending'):
+            assert (g['rows'][k].astype(np.int64) == want[k]).all(), (pol, k)
+        assert g['n_served'] == int(want['n_served'].sum()) and g['n_unserved'] == int(want['n_unserved'].sum())
+        assert g['wait_sum'] == int(want['wait_sum'].sum()) and g['wait_max'] == int(want['wait_max'].max())
+        assert g['pending_ticks'] == int(want['pending'].sum())
+        seen_wait += g['wait_sum']
+    assert seen_wait > 0
+    # the report carries the columns
+    res = autoscaler.replay.replay_fleet(llen.astype(np_t), pols, inprog=ip_dev, group_off=go,
+                                         cur0=cur0.astype(np.int32), patch_fail=fail, startup_delay=delay)
+    rep = autoscaler.replay.sweep_report(res, first_pod=got)
+    assert rep[1]['bursts_served'] == got[1]['n_served'] and rep[1]['mean_wait_seconds'] == got[1]['mean_wait'] * 5

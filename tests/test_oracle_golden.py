@@ -189,3 +189,25 @@ def test_python_and_c_oracle_agree_on_random_replays():
         assert res['dense'][0, :, 0].tolist() == after, case
         assert res['n_patches'][0, 0] == len(patches), case
         assert res['pod_ticks'][0, 0] == sum(after), case
+
+
+def test_first_pod_latency_against_the_reference_made_fixture():
+    """tests/golden/first_pod_cases.json: the reference's own scale() loop (read through its
+    get_current_pods, only_running under a start-up delay) with the reads before and after every
+    tick recorded, and the written definition applied to them.  Both oracle forms must agree."""
+    import numpy as np
+    from oracle import coracle, oracle
+    from tests import helpers
+    cases = helpers.golden_json('first_pod_cases')
+    assert len(cases) >= 80 and sum(c['stats']['n_unserved'] for c in cases) > 10
+    for c in cases:
+        want = c['stats']
+        got = oracle.first_pod_latency(c['depths'], None, c['kpp'], c['min'], c['max'], c['cur0'],
+                                       c['fails'], c['delay'])
+        assert got == want
+        depths = np.array(c['depths'], dtype=np.int32)
+        nq = depths.shape[1]
+        fails = None if c['fails'] is None else np.array(c['fails']).reshape(-1, 1)
+        cg = coracle.first_pod(depths, None, np.array([0, nq], dtype=np.uint64), np.array([c['cur0']], dtype=np.int32),
+                               (c['kpp'], c['min'], c['max']), patch_fail=fails, startup_delay=c['delay'])
+        assert {k: int(v[0]) for k, v in cg.items()} == want
