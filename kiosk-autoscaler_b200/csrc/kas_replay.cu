@@ -1252,28 +1252,30 @@ replay_grouped_tiled_kernel(const __grid_constant__ ReplayParams P) {
 //     exact 64-bit code.
 // Offsets that are not non-decreasing inside [0, Q], a group of 2048 queues or more, a run too
 // wide for a tile: that block reads the trace element by element with the exact arithmetic.
-#ifndef KAS_GS_STAGE_KB
-#define KAS_GS_STAGE_KB 12
+// Block sizes: 512 resources per block for fleets that fill the machine (a larger block sorts
+// a larger population, so more warps hold a single size class: 30.8 of 32 lanes busy against
+// 22.3 with 128; measured 1.37 ms against 1.72 ms per 8 GB), 128 for smaller fleets.  Stages:
+// 96 bytes per thread and stage, two stages for the large block, three for the small one.
+#ifndef KAS_GS_BIG_THREADS
+#define KAS_GS_BIG_THREADS 512
 #endif
-#ifndef KAS_GS_THREADS
-#define KAS_GS_THREADS 128
-#endif
-constexpr int kGsThreads = KAS_GS_THREADS;     // resources per block; a power of two
-#ifndef KAS_GS_UNROLL_SP4
-#define KAS_GS_UNROLL_SP4 0    /* unroll the queue loop under four policies per thread as well */
-#endif
-#ifndef KAS_GS_STAGES
-#define KAS_GS_STAGES 3
-#endif
-constexpr int kGsStages = KAS_GS_STAGES;       // tile buffers; kGsStages - 1 tiles are in flight
-constexpr uint32_t kGsStageBytes = KAS_GS_STAGE_KB * 1024;   // per stage and array
+constexpr int kGsSmallThreads = 128;
+constexpr int kGsBigThreads = KAS_GS_BIG_THREADS;
+constexpr uint32_t kGsStageBytesPerThread = 96;
 constexpr uint32_t kGsMaxTileTicks = 32;
 constexpr uint32_t kGsMaxOwn = 2048;          // queues of one resource: x kGsMaxPods stays below 2^31
 constexpr int32_t kGsMaxPods = 1 << 20;
+#ifndef KAS_GS_UNROLL_SP4
+#define KAS_GS_UNROLL_SP4 0    /* unroll the queue loop under four policies per thread as well (measured slower) */
+#endif
+constexpr uint32_t gs_stage_bytes(int threads) { return (uint32_t)threads * kGsStageBytesPerThread; }
+constexpr int gs_stages(int threads) { return threads >= 512 ? 2 : 3; }
 
-template <typename E, int SP, int IPMODE, bool K1>
+template <typename E, int SP, int IPMODE, bool K1, int kGsThreads>
 __global__ void __launch_bounds__(kGsThreads)
 replay_grouped_sorted_kernel(const __grid_constant__ ReplayParams P) {
+    constexpr int kGsStages = gs_stages(kGsThreads);          // tile buffers; kGsStages - 1 tiles are in flight
+    constexpr uint32_t kGsStageBytes = gs_stage_bytes(kGsThreads);   // per stage and array
     constexpr uint32_t kEPP = 16 / sizeof(E);
     constexpr uint32_t kStageVec = kGsStageBytes / 16;
     constexpr uint32_t kArrays = IPMODE == 2 ? 2u : 1u;
@@ -1427,6 +1429,9 @@ replay_grouped_sorted_kernel(const __grid_constant__ ReplayParams P) {
 #pragma unroll
                 for (int s = 0; s < SP; ++s) want[s] = clip64(sum[s], pol[s].mn, pol[s].mx, cur[s]);   // :259
             };
+            uint32_t own[8];                 // own[j] = 1 when queue j of the unrolled loop is this resource's
+#pragma unroll
+            for (int j = 0; j < 8; ++j) own[j] = (uint32_t)j < n_own ? (uint32_t)P.one : 0u;
             auto run_tile = [&](auto ntag) {
                 constexpr int N = decltype(ntag)::value;                  // queues per resource, 0: not known here
                 for (uint32_t t = 0; t < nt; ++t) {
@@ -1438,7 +1443,9 @@ replay_grouped_sorted_kernel(const __grid_constant__ ReplayParams P) {
                     uint32_t any = 0u;
                     // `live_q`: the queue is this resource's own (a lane with fewer queues than the
                     // warp's largest group reads on into its neighbour's and adds nothing)
-                    auto one_queue = [&](uint32_t j, bool live_q) {
+                    // (the add is a multiply-add by 0 or 1: the integer ALU pipe, which runs at half the
+                    // FMA pipe's rate, is what this kernel fills first)
+                    auto one_queue = [&](uint32_t j, uint32_t live_q) {
                         uint32_t tally = (uint32_t)lrow[j];
                         if constexpr (kCheck) any |= tally;
                         if constexpr (IPMODE == 1) tally += (uint32_t)iq[j];          // range-checked when staged
@@ -1452,14 +1459,14 @@ replay_grouped_sorted_kernel(const __grid_constant__ ReplayParams P) {
                             const uint32_t q = K1 ? tally : quotient_small(tally + 1u, pol[s]);
                             const uint32_t v = (uint32_t)finish_simple3(q, __viaddmin_u32(q, keep[s].add, keep[s].lim),
                                                                         pol[s], cur[s]);                     // :255-257
-                            if (live_q) sum[s] += v;
+                            sum[s] = v * live_q + sum[s];
                         }
                     };
                     if constexpr (N > 0) {
 #pragma unroll
-                        for (int j = 0; j < N; ++j) one_queue((uint32_t)j, (uint32_t)j < n_own);
+                        for (int j = 0; j < N; ++j) one_queue((uint32_t)j, own[j < 8 ? j : 0]);
                     } else {
-                        for (uint32_t j = 0; j < n_own; ++j) one_queue(j, true);
+                        for (uint32_t j = 0; j < n_own; ++j) one_queue(j, 1u);
                     }
                     int32_t want[SP];
                     if (kCheck && any >= kSmallTallyTerm) {
@@ -1633,28 +1640,34 @@ static int launch_grouped(const ReplayParams &P, int mode, cudaStream_t stream) 
 #endif
     if (lean) {
         const bool k1 = SP == 1 && P.pol[0].k1 != 0u;
-        const unsigned gs_grid = (unsigned)(((P.R + kGsThreads - 1) / kGsThreads) * ny);
-        // (+ 64 bytes: a lane may read up to seven elements past the last staged row)
-        const size_t smem = (size_t)kGsStages * (tickip ? 2 : 1) * kGsStageBytes +
-                            (P.inprog_mode == 1 ? (size_t)kGsStageBytes / sizeof(E) * 4 : 0) + 64;
-#define KAS_LAUNCH_GS(IPM, KONE)                                                                   \
+        const bool big = P.R >= (uint64_t)kGsBigThreads * 148u;
+#define KAS_LAUNCH_GS(IPM, KONE, TH)                                                               \
     do {                                                                                           \
-        auto kern = replay_grouped_sorted_kernel<E, SP, IPM, KONE>;                                \
+        /* (+ 64 bytes: a lane may read up to seven elements past the last staged row) */          \
+        const size_t smem = (size_t)gs_stages(TH) * (tickip ? 2 : 1) * gs_stage_bytes(TH) +       \
+                            (P.inprog_mode == 1 ? (size_t)gs_stage_bytes(TH) / sizeof(E) * 4 : 0) + 64; \
+        const unsigned gs_grid = (unsigned)(((P.R + TH - 1) / TH) * ny);                          \
+        auto kern = replay_grouped_sorted_kernel<E, SP, IPM, KONE, TH>;                            \
         KAS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
                                           (int)smem));                                             \
-        kern<<<gs_grid, kGsThreads, smem, stream>>>(P);                                            \
+        kern<<<gs_grid, TH, smem, stream>>>(P);                                                    \
+    } while (0)
+#define KAS_LAUNCH_GS_T(IPM, KONE)                                                                 \
+    do {                                                                                           \
+        if (big) KAS_LAUNCH_GS(IPM, KONE, kGsBigThreads); else KAS_LAUNCH_GS(IPM, KONE, kGsSmallThreads); \
     } while (0)
         if constexpr (SP == 1) {
             if (k1) {
-                if (P.inprog_mode == 0) KAS_LAUNCH_GS(0, true);
-                else if (P.inprog_mode == 1) KAS_LAUNCH_GS(1, true);
-                else KAS_LAUNCH_GS(2, true);
+                if (P.inprog_mode == 0) KAS_LAUNCH_GS_T(0, true);
+                else if (P.inprog_mode == 1) KAS_LAUNCH_GS_T(1, true);
+                else KAS_LAUNCH_GS_T(2, true);
                 return KAS_OK;
             }
         }
-        if (P.inprog_mode == 0) KAS_LAUNCH_GS(0, false);
-        else if (P.inprog_mode == 1) KAS_LAUNCH_GS(1, false);
-        else KAS_LAUNCH_GS(2, false);
+        if (P.inprog_mode == 0) KAS_LAUNCH_GS_T(0, false);
+        else if (P.inprog_mode == 1) KAS_LAUNCH_GS_T(1, false);
+        else KAS_LAUNCH_GS_T(2, false);
+#undef KAS_LAUNCH_GS_T
 #undef KAS_LAUNCH_GS
         return KAS_OK;
     }

@@ -540,6 +540,43 @@ def test_grouped_lean_kernel(pol, groups, dtype, ipmode):
     assert R == got.pod_ticks.shape[0]
 
 
+@pytest.mark.parametrize('pol', ['k1', 'kpp', 'four'])
+@pytest.mark.parametrize('dtype', ['int32', 'uint16'])
+@pytest.mark.parametrize('ipmode', [0, 1, 2])
+def test_grouped_lean_kernel_large_fleet(pol, dtype, ipmode):
+    """A fleet large enough for the 512-resource blocks of the lean multi-queue kernel (two tile
+    buffers instead of three), including a block with a too-wide group and large counts."""
+    import autoscaler
+    from oracle import coracle
+    rng = np.random.default_rng(stable_seed('lean-big', pol, dtype, ipmode))
+    T, Q = 40, 420_000
+    go = _group_offsets(rng, Q, list(range(1, 9)))
+    go = go[(go < 100_000) | (go > 102_500)].astype(np.uint64)      # one resource of ~2500 queues
+    assert len(go) - 1 >= 512 * 148
+    hi = 2 ** 16 - 1 if dtype == 'uint16' else 2 ** 31 - 1
+    llen = rng.integers(0, 60, size=(T, Q)).astype(np.int64)
+    llen[rng.random(llen.shape) < 0.4] = 0
+    llen[rng.random(llen.shape) < 0.0005] = hi
+    if dtype == 'int32':
+        llen[rng.random(llen.shape) < 0.0005] = -3
+    np_t = np.uint16 if dtype == 'uint16' else np.int32
+    inprog = ip_dev = None
+    if ipmode == 1:
+        inprog = rng.integers(0, 5, size=Q).astype(np.int64)
+        inprog[rng.integers(0, Q, size=5)] = 70000
+        ip_dev = inprog.astype(np.int32)
+    elif ipmode == 2:
+        inprog = rng.integers(0, 9, size=(T, Q)).astype(np.int64)
+        ip_dev = inprog.astype(np_t)
+    pols = LEAN_POLICIES[pol]
+    want = coracle.replay(llen.astype(np.int32), None if inprog is None else inprog.astype(np.int32), go, None, pols)
+    got = autoscaler.replay.replay_fleet(llen.astype(np_t), pols, inprog=ip_dev, group_off=go)
+    assert (got.pod_ticks == want['pod_ticks']).all()
+    assert (got.n_patches == want['n_patches']).all()
+    assert (got.final == want['final']).all()
+    assert (got.sums[:, 0] == want['pod_ticks'].sum(0)).all()
+
+
 def test_grouped_offsets_that_overlap_or_go_back():
     """CSR offsets straight through the C ABI that are not non-decreasing: the lean kernel's
     blocks notice and read element by element, like the plain kernel and the oracle (a range
