@@ -95,6 +95,20 @@ KAS_API int kas_pack_heads_host(const uint8_t *blob, const uint64_t *off, uint64
 KAS_API int kas_index_lines_host(const uint8_t *blob, uint64_t blob_len, uint64_t *off,
                          uint64_t off_cap, uint64_t *n_keys);
 
+/* Keys of a Redis RDB dump (the keyspace at rest instead of a SCAN over TCP, autoscaler.py:67-71).
+ * Walks the dump once, skipping values by type: key i is out_blob[out_off[i] .. out_off[i+1])
+ * (integer-encoded keys as their decimal text, LZF-compressed keys decompressed), out_type[i] its
+ * RDB value type, out_db[i] its database, out_list_len[i] the number of elements when the key
+ * holds a list -- what LLEN would answer (autoscaler.py:67) -- or UINT64_MAX when a list node's
+ * 16-bit counter is saturated; 0 for other types.  Every output pointer may be NULL (call once with
+ * NULLs to size the buffers: *n_keys, *blob_len); out_off has n_keys+1 entries (off_cap is its
+ * capacity in elements), blob_cap the capacity of out_blob.  RDB versions 1-12; value types 0-5, 7,
+ * 9-21.  KAS_ERR_INVALID: not an RDB file, truncated or malformed; KAS_ERR_UNSUPPORTED: an opcode
+ * or value type this reader does not know (the dump is never half-read); KAS_ERR_TOO_SMALL. */
+KAS_API int kas_rdb_keys_host(const uint8_t *rdb, uint64_t rdb_len, uint8_t *out_blob, uint64_t blob_cap,
+                              uint64_t *out_off, uint64_t off_cap, uint8_t *out_type, uint32_t *out_db,
+                              uint64_t *out_list_len, uint64_t *n_keys, uint64_t *blob_len);
+
 /* Device packer for a blob already resident in HBM.  d_heads must be 16-byte
  * aligned.  Reads every key's first min(len, rec_bytes) bytes. */
 KAS_API int kas_pack_heads(const uint8_t *d_blob, const uint64_t *d_off, uint64_t n_keys,

@@ -101,6 +101,9 @@ SYMBOLS = {
                                       C.c_void_p, C.c_int]),
     'kas_index_lines_host': (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
                                        C.POINTER(C.c_uint64)]),
+    'kas_rdb_keys_host': (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
+                                    C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64),
+                                    C.POINTER(C.c_uint64)]),
     'kas_pack_heads': (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32,
                                  C.c_void_p, C.c_void_p]),
     'kas_prefix_table_bytes': (C.c_size_t, [C.c_uint32, C.c_uint32]),
@@ -266,6 +269,29 @@ def index_lines_host(blob):
     check(lib().kas_index_lines_host(np_ptr(blob), blob.size, np_ptr(off), off.size, C.byref(n)),
           'kas_index_lines_host')
     return off
+
+
+RDB_LIST_TYPES = frozenset((1, 10, 14, 18))
+RDB_UNKNOWN_LEN = 0xFFFFFFFFFFFFFFFF
+
+
+def rdb_keys_host(data):
+    """Keys of an RDB dump (bytes-like).  Returns dict(blob uint8, off uint64 [n+1], type uint8 [n],
+    db uint32 [n], list_len uint64 [n])."""
+    rdb = np.frombuffer(data, dtype=np.uint8)
+    n, nbytes = C.c_uint64(0), C.c_uint64(0)
+    check(lib().kas_rdb_keys_host(np_ptr(rdb), rdb.size, None, 0, None, 0, None, None, None,
+                                  C.byref(n), C.byref(nbytes)), 'kas_rdb_keys_host')
+    blob = np.empty(max(1, nbytes.value), dtype=np.uint8)
+    off = np.empty(n.value + 1, dtype=np.uint64)
+    typ = np.empty(max(1, n.value), dtype=np.uint8)
+    db = np.empty(max(1, n.value), dtype=np.uint32)
+    llen = np.empty(max(1, n.value), dtype=np.uint64)
+    check(lib().kas_rdb_keys_host(np_ptr(rdb), rdb.size, np_ptr(blob), blob.size, np_ptr(off), off.size,
+                                  np_ptr(typ), np_ptr(db), np_ptr(llen), C.byref(n), C.byref(nbytes)),
+          'kas_rdb_keys_host')
+    return dict(blob=blob[:nbytes.value], off=off, type=typ[:n.value], db=db[:n.value],
+                list_len=llen[:n.value])
 
 
 def synth_keys_host(seed, first_key, n_keys, names, long_tail=False, rec_bytes=0,

@@ -50,6 +50,37 @@ class KeySnapshot(object):
         return cls(blob=blob, off=engine.index_lines_host(blob), sep_bytes=1)
 
     @classmethod
+    def from_rdb(cls, data, db=None):
+        """From a Redis RDB dump (bytes, or a path): every key of the dump -- of database
+        ``db`` only when given -- without a server (``kas_rdb_keys_host``: values are skipped by
+        type, LZF-compressed and integer-encoded keys restored).  The snapshot also carries
+        ``list_lengths``: {key bytes: elements} for the keys that hold lists, i.e. what ``LLEN``
+        would answer (autoscaler.py:67 of the reference)."""
+        if isinstance(data, str):
+            with open(data, 'rb') as f:
+                data = f.read()
+        d = engine.rdb_keys_host(data)
+        off = d['off']
+        keep = np.ones(len(d['type']), dtype=bool) if db is None else d['db'] == db
+        lens = np.diff(off.astype(np.int64))
+        if not keep.all():
+            idx = np.flatnonzero(keep)
+            parts = [d['blob'][off[i]:off[i + 1]] for i in idx]
+            blob = np.concatenate(parts + [np.zeros(1, np.uint8)]) if len(parts) else np.zeros(1, np.uint8)
+            new_off = np.zeros(len(idx) + 1, dtype=np.uint64)
+            new_off[1:] = np.cumsum(lens[idx])
+        else:
+            idx = np.arange(len(lens))
+            blob, new_off = d['blob'], off
+        snap = cls(blob=blob, off=new_off)
+        snap.list_lengths = {}
+        for j, i in enumerate(idx):
+            if int(d['type'][i]) in engine.RDB_LIST_TYPES:
+                n = int(d['list_len'][i])
+                snap.list_lengths[bytes(blob[new_off[j]:new_off[j + 1]])] = None if n == engine.RDB_UNKNOWN_LEN else n
+        return snap
+
+    @classmethod
     def from_heads(cls, heads):
         """From already packed heads: uint8 [n][rec_bytes] numpy array or tensor."""
         return cls(heads=heads)
@@ -400,6 +431,20 @@ class SnapshotRedis(object):
     def __init__(self, snapshot=None, lists=None):
         self.snapshot = snapshot if snapshot is not None else KeySnapshot.from_keys([])
         self.lists = dict(lists or {})
+
+    @classmethod
+    def from_rdb(cls, data, db=0):
+        """The whole seam from one RDB dump: the keyspace for the SCAN term and the lengths of
+        the list keys for ``llen`` (a key that is absent or not a list answers 0 here; the live
+        server raises WRONGTYPE for a non-list, which the reference re-raises, redis.py:194-195)."""
+        snap = KeySnapshot.from_rdb(data, db=db)
+        lists = {}
+        for k, n in snap.list_lengths.items():
+            if n is None:
+                raise ValueError('list %r has a node with a saturated element counter; its LLEN is not '
+                                 'in the dump header' % (k,))
+            lists[k.decode('utf-8', 'surrogateescape')] = n
+        return cls(snap, lists)
 
     def llen(self, name):
         return int(self.lists.get(name, 0))

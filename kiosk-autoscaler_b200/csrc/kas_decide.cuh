@@ -89,6 +89,13 @@ __device__ __forceinline__ uint32_t quotient_simple(uint32_t tally, const PolDev
 __device__ __forceinline__ uint32_t quotient_small(uint32_t tally_plus_1, const PolDev &p) {
     return __umulhi(tally_plus_1, p.m32);
 }
+// The same quotient with the round-up magic number m_up = ceil(2^32 / kpp) = m32 + 1, which needs
+// no + 1 on the dividend: exact for tally < 2^17 and 2 <= kpp <= 2^14 (the error term
+// tally * (m_up * kpp - 2^32) stays below 2^32; checked exhaustively in tests/test_host_logic.py).
+// kpp == 1 has no 32-bit m_up; its quotient is the tally.
+__device__ __forceinline__ uint32_t quotient_up(uint32_t tally, uint32_t m_up) {
+    return __umulhi(tally, m_up);
+}
 __device__ __forceinline__ int32_t finish_simple(uint32_t q, const PolDev &p, int32_t cur) {
     // if/elif clamp with 0 <= max and min <= max: the unsigned min already lands in
     // [0, max], so no saturation of q is needed before the signed max with min

@@ -7,7 +7,7 @@ cd "$(dirname "$0")/../.."
 name=$1; shift
 out=build/variants; mkdir -p $out/obj_$name
 objs=""
-for s in kas_match kas_replay kas_events kas_glob kas_ingest kas_comm; do
+for s in kas_match kas_replay kas_events kas_glob kas_ingest kas_comm kas_rdb; do
   /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 \
     -Xcompiler -fPIC,-fvisibility=hidden,-Wall --expt-relaxed-constexpr "$@" \
     -c kiosk-autoscaler_b200/csrc/$s.cu -o $out/obj_$name/$s.o &

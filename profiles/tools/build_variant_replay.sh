@@ -11,5 +11,5 @@ lib=kiosk-autoscaler_b200/lib
   -Xcompiler -fPIC,-fvisibility=hidden,-Wall --expt-relaxed-constexpr "$@" \
   -c kiosk-autoscaler_b200/csrc/kas_replay.cu -o $out/obj_$name/kas_replay.o
 /usr/local/cuda/bin/nvcc -shared -gencode arch=compute_100a,code=sm_100a -o $out/libkas_$name.so \
-  $out/obj_$name/kas_replay.o $lib/kas_match.o $lib/kas_events.o $lib/kas_glob.o $lib/kas_ingest.o $lib/kas_comm.o -ldl
+  $out/obj_$name/kas_replay.o $lib/kas_match.o $lib/kas_events.o $lib/kas_glob.o $lib/kas_ingest.o $lib/kas_comm.o $lib/kas_rdb.o -ldl
 echo $out/libkas_$name.so
