@@ -127,13 +127,17 @@ def measured_peak():
         return 6650.0, 'fallback (B200_PROFILING.md)'
 
 
-def ncu_traffic(kernel):
-    """DRAM bytes per launch from the committed ncu capture summary, or None."""
+def ncu_traffic(kernel, alg_bytes):
+    """DRAM bytes per launch from the committed ncu capture of this kernel, if the capture was made
+    on a launch of this size (profiles/traffic.json); else None."""
     try:
         with open(os.path.join(ROOT, 'profiles', 'traffic.json')) as f:
-            return json.load(f).get(kernel)
+            e = json.load(f).get(kernel)
+        if isinstance(e, dict) and abs(e['algorithmic_bytes'] - alg_bytes) <= 0.001 * alg_bytes:
+            return e['bytes']
     except Exception:
-        return None
+        pass
+    return None
 
 
 class ClockSampler(threading.Thread):
@@ -345,7 +349,7 @@ class Ctx(object):
         return {'bound': 'hbm', 'kernel': kernel, 'achieved': gbs, 'peak': self.peak, 'unit': 'GB/s',
                 'frac': gbs / self.peak, 'peak_source': self.peak_src,
                 'algorithmic_bytes_per_launch': int(alg_bytes), 'kernel_ms': ms,
-                'traffic': ncu_traffic(traffic_key) if traffic_key else None}
+                'traffic': ncu_traffic(traffic_key, alg_bytes) if traffic_key else None}
 
 
 def bind_to_gpu_numa_node(local):
@@ -703,7 +707,7 @@ def replay_leg(cx, cfg, headline, sampler):
         del o16, oS16
         k16 = 'replay_grouped_sorted_kernel' if cfg['grouped'] else 'replay_packed16_kernel'
         rep['s1_uint16'] = {'policies': 1, 'ms': ms16, 'decisions_per_sec': dps16,
-                            'roofline': cx.roofline(k16, Q * T * 2, ms16)}
+                            'roofline': cx.roofline(k16, Q * T * 2, ms16, k16)}
         rep['sweep_uint16'] = {'policies': len(SWEEP), 'ms': msS16, 'decisions_per_sec': dpsS16, 'reps': 5, 'warmup': 2}
     del trace
 
@@ -895,7 +899,7 @@ def extras_leg(cx, cfg, tally):
         grouped[dt] = {'s1_ms': ms1, 's1_queue_ticks_per_sec': Qg * Tg / (ms1 * 1e-3),
                        'four_policies_ms': ms4, 'four_policies_decisions_per_sec': 4 * Qg * Tg / (ms4 * 1e-3),
                        'oracle_equal_on_samples': True,
-                       'roofline': cx.roofline('replay_grouped_sorted_kernel', Qg * Tg * esz, ms1)}
+                       'roofline': cx.roofline('replay_grouped_sorted_kernel', Qg * Tg * esz, ms1, 'replay_grouped_sorted_kernel')}
         del o, tot
     out['multi_queue_fleet'] = {'queues': Qg, 'resources': R, 'ticks': Tg, 'group_sizes': '1-8', **grouped}
     del trace, d_go

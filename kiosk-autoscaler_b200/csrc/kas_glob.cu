@@ -15,12 +15,29 @@
 // per-pattern counts by warp ballot + popc.  The matcher is iterative: a mismatch
 // after a '*' resumes one byte further behind the LAST star, which is equivalent
 // to the server's recursive search for these pattern elements.
+// The keys of a block's batch (256 consecutive keys = one contiguous run of the blob) are
+// copied to shared memory with coalesced 16-byte loads first, so the byte-by-byte walk of
+// every pattern reads shared memory instead of issuing dependent one-byte global loads; a
+// batch whose bytes do not fit (very long keys) is matched straight from global memory.
 #include "kas_common.cuh"
 
 namespace kas {
 
 constexpr int kGlobThreads = 256;
 constexpr uint32_t kGlobMaxPatternBytes = 16 * 1024;
+constexpr uint32_t kGlobStageBytes = 32 * 1024;     // key bytes of one batch staged in shared memory
+
+// One key byte: from shared memory (a 32-bit shared address) or from global memory.
+template <bool SHARED>
+__device__ __forceinline__ uint8_t key_byte(const uint8_t *s, uint32_t saddr, uint64_t i) {
+    if constexpr (SHARED) {
+        uint32_t v;
+        asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(saddr + (uint32_t)i));
+        return (uint8_t)v;
+    } else {
+        return __ldg(s + i);
+    }
+}
 
 // Does pattern element at p[pi..] match byte c?  Advances pi past the element.
 // Mirrors the class / escape / literal cases of the server's matcher.
@@ -63,7 +80,8 @@ __device__ __forceinline__ bool glob_element(const uint8_t *p, uint32_t plen, ui
     return e == c;
 }
 
-__device__ bool glob_match(const uint8_t *p, uint32_t plen, const uint8_t *s, uint64_t slen) {
+template <bool SHARED>
+__device__ bool glob_match(const uint8_t *p, uint32_t plen, const uint8_t *s, uint32_t saddr, uint64_t slen) {
     uint32_t pi = 0, star_pi = 0xFFFFFFFFu;
     uint64_t si = 0, star_si = 0;
     while (si < slen) {
@@ -77,7 +95,7 @@ __device__ bool glob_match(const uint8_t *p, uint32_t plen, const uint8_t *s, ui
         }
         if (pi < plen) {
             uint32_t next = pi;
-            if (glob_element(p, plen, next, __ldg(s + si))) {
+            if (glob_element(p, plen, next, key_byte<SHARED>(s, saddr, si))) {
                 pi = next;
                 ++si;
                 continue;
@@ -109,6 +127,9 @@ glob_count_kernel(const uint8_t *__restrict__ blob, const uint64_t *__restrict__
     __syncthreads();
 
     const uint32_t lane = threadIdx.x & 31u;
+    // the staging area: 16-byte aligned, behind the pattern bytes
+    uint8_t *s_keys = gsm + (((2 * n_patterns + 1) * 4 + total + 15u) & ~15u);
+    const uint32_t s_keys_addr = (uint32_t)__cvta_generic_to_shared(s_keys);
     for (uint64_t base = (uint64_t)blockIdx.x * blockDim.x; base < n_keys; base += (uint64_t)gridDim.x * blockDim.x) {
         const uint64_t i = base + threadIdx.x;
         const bool live = i < n_keys;
@@ -118,12 +139,27 @@ glob_count_kernel(const uint8_t *__restrict__ blob, const uint64_t *__restrict__
             const uint64_t span = off[i + 1] - a;
             len = span > sep_bytes ? span - sep_bytes : 0;
         }
+        // the batch's run of the blob, widened to 16-byte boundaries
+        const uint64_t last = min(base + (uint64_t)blockDim.x, n_keys);
+        const uint64_t b0 = off[base], b1 = off[last];
+        const uintptr_t g0 = (reinterpret_cast<uintptr_t>(blob) + b0) & ~(uintptr_t)15;
+        const uintptr_t g1 = (reinterpret_cast<uintptr_t>(blob) + b1 + 15) & ~(uintptr_t)15;
+        const bool staged = b1 >= b0 && g1 - g0 <= kGlobStageBytes;          // uniform over the block
+        if (staged) {
+            const uint32_t pieces = (uint32_t)((g1 - g0) / 16);
+            for (uint32_t k = threadIdx.x; k < pieces; k += blockDim.x)
+                reinterpret_cast<uint4 *>(s_keys)[k] = ldg_stream_128(reinterpret_cast<const uint4 *>(g0) + k);
+            __syncthreads();
+        }
+        const uint32_t my = s_keys_addr + (uint32_t)(reinterpret_cast<uintptr_t>(blob) + a - g0);
         for (uint32_t q = 0; q < n_patterns; ++q) {       // warp-uniform loop
             const uint32_t pa = s_off[q], pl = s_off[q + 1] - pa;
-            const bool m = live && glob_match(s_pat + pa, pl, blob + a, len);
+            const bool m = live && (staged ? glob_match<true>(s_pat + pa, pl, nullptr, my, len)
+                                           : glob_match<false>(s_pat + pa, pl, blob + a, 0u, len));
             const uint32_t votes = __ballot_sync(0xFFFFFFFFu, m);
             if (lane == 0 && votes) atomicAdd(&s_hist[q], (uint32_t)__popc(votes));
         }
+        if (staged) __syncthreads();                      // the next batch overwrites the staging area
     }
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < n_patterns; i += blockDim.x) {
@@ -150,7 +186,9 @@ int kas_glob_count(const uint8_t *d_blob, const uint64_t *d_off, uint64_t n_keys
     if (n_keys == 0) return KAS_OK;
     const int sms = sm_count();
     if (sms <= 0) return KAS_ERR_CUDA;
-    const size_t smem = (2 * (size_t)n_patterns + 1) * sizeof(uint32_t) + pattern_bytes;
+    const size_t smem = (((2 * (size_t)n_patterns + 1) * sizeof(uint32_t) + pattern_bytes + 15) & ~(size_t)15) +
+                        kGlobStageBytes;
+    KAS_CUDA_TRY(cudaFuncSetAttribute(glob_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     uint64_t grid = (n_keys + kGlobThreads - 1) / kGlobThreads;
     if (grid > (uint64_t)sms * 8) grid = (uint64_t)sms * 8;
     glob_count_kernel<<<(unsigned)grid, kGlobThreads, smem, stream>>>(

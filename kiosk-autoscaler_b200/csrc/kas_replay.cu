@@ -513,6 +513,9 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
+#ifndef KAS_SWEEP_FMA_ADDS
+#define KAS_SWEEP_FMA_ADDS 0   // packed form: patch / pod-tick sums of a tile as IMAD instead of VIADD.16x2
+#endif
 #ifndef KAS_SWEEP_TMA
 #define KAS_SWEEP_TMA 1   // stage tiles with bulk asynchronous copies (TMA, cp.async.bulk + mbarrier); 0: cp.async
 #endif
@@ -625,6 +628,16 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
         for (int p = 0; p < VEC / 2; ++p) { cur2[s][p] = 0u; np2[s][p] = 0u; pa2[s][p] = 0u; }
     }
     const uint32_t add2 = keep.add * 0x00010001u;
+    // PACKED: 65536 as a value the compiler cannot see through, so that taking a 32-bit word of
+    // the uint16 trace apart (w >> 16, w - (w >> 16 << 16)) and putting two quotients together
+    // (hi * 65536 + lo) are multiplies on the FMA pipe: the integer ALU pipe is this kernel's limit
+    const uint32_t k64k = 65536u * (uint32_t)one;
+    const uint32_t m_up = pol[0].m32 + 1u;      // ceil(2^32 / keys_per_pod), keys_per_pod >= 2 (see quotient_up)
+    const bool kpp_one = pol[0].k1 != 0u;
+    // per-queue in-progress counts as packed pairs, and whether they fit the packed form at all
+    uint32_t ipq2[VEC / 2];
+#pragma unroll
+    for (int p = 0; p < VEC / 2; ++p) ipq2[p] = (uint32_t)ipq[2 * p] | ((uint32_t)ipq[2 * p + 1] << 16);
 
     const uint32_t n_tiles = (T + tile_ticks - 1) / tile_ticks;
 #if KAS_SWEEP_TMA
@@ -713,6 +726,116 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
             auto ticks = [&](uint32_t t, auto gtag, auto densetag) {
                 constexpr int G = decltype(gtag)::value;
                 constexpr bool DENSE = decltype(densetag)::value;   // chosen per tile, so the tick code has no branch
+                // PACKED: two resources per instruction (min / max3 / add on 16-bit halves, sm_100's
+                // VIMNMX.U16x2, VIMNMX3.S16x2, VIADDMNMX.U16x2, VIADD.16x2).  Per pair of resources the
+                // policies of the warp share the quotients, packed q2, and the keep factors as a mask km2
+                // (0xFFFF where keep == 1); per policy: min with max_pods, the three-input maximum with
+                // min_pods and the kept current pods, and the two sums of the tile.
+                auto run_packed = [&](const uint32_t (&q2)[G][VEC / 2]) {
+#pragma unroll
+                    for (int g = 0; g < G; ++g) {
+                        uint32_t km2[VEC / 2];
+#pragma unroll
+                        for (int p = 0; p < VEC / 2; ++p)
+                            km2[p] = __viaddmin_u16x2(q2[g][p], add2, 0x00010001u) * 0xFFFFu;
+#pragma unroll
+                        for (int s = 0; s < SP; ++s) {
+#pragma unroll
+                            for (int p = 0; p < VEC / 2; ++p) {
+                                const uint32_t c2 = cur2[s][p];
+                                const uint32_t w2 = __vimax3_s16x2(__vminu2(q2[g][p], mx2[s]), mn2[s], c2 & km2[p]);   // :255-259
+#if KAS_SWEEP_FMA_ADDS
+                                // the two sums of the tile as multiply-adds (no carry crosses the halves)
+                                np2[s][p] = __vminu2(w2 ^ c2, 0x00010001u) * (uint32_t)one + np2[s][p];             // :227
+                                pa2[s][p] = w2 * (uint32_t)one + pa2[s][p];
+#else
+                                np2[s][p] = __vadd2(np2[s][p], __vminu2(w2 ^ c2, 0x00010001u));                     // :227
+                                pa2[s][p] = __vadd2(pa2[s][p], w2);
+#endif
+                                cur2[s][p] = w2;
+                            }
+                            if (DENSE && live[s]) {
+                                int32_t *o = P.dense + ((uint64_t)P.pol_index[pbase + s] * T + t0 + t + g) * P.R + r0;
+                                *reinterpret_cast<int4 *>(o) = make_int4((int32_t)(cur2[s][0] & 0xFFFFu), (int32_t)(cur2[s][0] >> 16),
+                                                                         (int32_t)(cur2[s][1] & 0xFFFFu), (int32_t)(cur2[s][1] >> 16));
+                            }
+                        }
+                    }
+                };
+                if constexpr (PACKED) {
+                    // The common batch -- every count below 2^14 -- never leaves the packed form: the
+                    // tallies are formed as pairs straight from the staged rows (a 32-bit word of a
+                    // uint16 trace IS a pair), the quotients pair by pair.
+                    uint32_t q2[G][VEC / 2];
+                    uint32_t big = (uint32_t)ipq_sign;
+                    if constexpr (sizeof(E) == 2) {
+                        uint32_t w[G][VEC / 2];
+#pragma unroll
+                        for (int g = 0; g < G; ++g) {
+                            const uint2 a = *reinterpret_cast<const uint2 *>(tl + (t + g) * row_elems);
+                            w[g][0] = a.x; w[g][1] = a.y;
+                            big |= (a.x | a.y) & 0xC000C000u;
+                            if (TICKIP) {
+                                const uint2 b = *reinterpret_cast<const uint2 *>(ti + (t + g) * row_elems);
+                                big |= (b.x | b.y) & 0xC000C000u;
+                                w[g][0] += b.x; w[g][1] += b.y;            // halves below 2^15: no carry between them
+                            } else {
+                                w[g][0] += ipq2[0]; w[g][1] += ipq2[1];    // (zero without a per-queue term)
+                            }
+                        }
+                        if (__all_sync(working, big < kSweepPackedTallyTerm)) {
+#pragma unroll
+                            for (int g = 0; g < G; ++g)
+#pragma unroll
+                                for (int p = 0; p < VEC / 2; ++p) {
+                                    if (kpp_one) {
+                                        q2[g][p] = w[g][p];                                    // tally // 1, both halves
+                                    } else {
+                                        const uint32_t hi = __umulhi(w[g][p], k64k);           // w >> 16
+                                        const uint32_t lo = w[g][p] - hi * k64k;
+                                        q2[g][p] = quotient_up(hi, m_up) * k64k + quotient_up(lo, m_up);
+                                    }
+                                }
+                            run_packed(q2);
+                            return;
+                        }
+                    } else {
+                        uint32_t x[G][VEC];
+#pragma unroll
+                        for (int g = 0; g < G; ++g) {
+                            const int4 a = *reinterpret_cast<const int4 *>(tl + (t + g) * row_elems);
+                            x[g][0] = (uint32_t)a.x; x[g][1] = (uint32_t)a.y; x[g][2] = (uint32_t)a.z; x[g][3] = (uint32_t)a.w;
+                            big |= (uint32_t)(a.x | a.y | a.z | a.w);
+                            if (TICKIP) {
+                                const int4 b = *reinterpret_cast<const int4 *>(ti + (t + g) * row_elems);
+                                big |= (uint32_t)(b.x | b.y | b.z | b.w);
+                                x[g][0] += (uint32_t)b.x; x[g][1] += (uint32_t)b.y; x[g][2] += (uint32_t)b.z; x[g][3] += (uint32_t)b.w;
+                            } else {
+#pragma unroll
+                                for (int v = 0; v < VEC; ++v) x[g][v] += (uint32_t)ipq[v];
+                            }
+                        }
+                        if (__all_sync(working, big < kSweepPackedTallyTerm)) {
+#pragma unroll
+                            for (int g = 0; g < G; ++g)
+#pragma unroll
+                                for (int p = 0; p < VEC / 2; ++p) {
+                                    if (kpp_one) q2[g][p] = x[g][2 * p + 1] * k64k + x[g][2 * p];
+                                    else q2[g][p] = quotient_up(x[g][2 * p + 1], m_up) * k64k + quotient_up(x[g][2 * p], m_up);
+                                }
+                            run_packed(q2);
+                            return;
+                        }
+                    }
+                    // a count too large (or negative): this batch unpacked
+#pragma unroll
+                    for (int s = 0; s < SP; ++s)
+#pragma unroll
+                        for (int p = 0; p < VEC / 2; ++p) {
+                            cur[s][2 * p] = (int32_t)(cur2[s][p] & 0xFFFFu);
+                            cur[s][2 * p + 1] = (int32_t)(cur2[s][p] >> 16);
+                        }
+                }
                 int32_t l[G][VEC], ip[G][VEC];
                 int32_t any = ipq_sign;
 #pragma unroll
@@ -774,54 +897,6 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
                         }
                     }
                 };
-                // PACKED: two resources per instruction (min / max3 / add on 16-bit halves, sm_100's
-                // VIMNMX.U16x2, VIMNMX3.S16x2, VIADDMNMX.U16x2, VIADD.16x2).  Per pair of resources the
-                // pair of policies shares the quotients, packed q2, and the keep factors as a mask km2
-                // (0xFFFF where keep == 1); per policy: min with max_pods, the three-input maximum with
-                // min_pods and the kept current pods, and the two sums of the tile.
-                auto run_packed = [&]() {
-#pragma unroll
-                    for (int g = 0; g < G; ++g) {
-                        uint32_t q2[VEC / 2], km2[VEC / 2];
-#pragma unroll
-                        for (int p = 0; p < VEC / 2; ++p) {
-                            const uint32_t qa = quotient_small((uint32_t)l[g][2 * p] + (uint32_t)ip[g][2 * p] + 1u, pol[0]);
-                            const uint32_t qb = quotient_small((uint32_t)l[g][2 * p + 1] + (uint32_t)ip[g][2 * p + 1] + 1u, pol[0]);
-                            q2[p] = __byte_perm(qa, qb, 0x5410);                       // both below 2^15
-                            km2[p] = __viaddmin_u16x2(q2[p], add2, 0x00010001u) * 0xFFFFu;
-                        }
-#pragma unroll
-                        for (int s = 0; s < SP; ++s) {
-#pragma unroll
-                            for (int p = 0; p < VEC / 2; ++p) {
-                                const uint32_t c2 = cur2[s][p];
-                                const uint32_t w2 = __vimax3_s16x2(__vminu2(q2[p], mx2[s]), mn2[s], c2 & km2[p]);   // :255-259
-                                np2[s][p] = __vadd2(np2[s][p], __vminu2(w2 ^ c2, 0x00010001u));                  // :227
-                                pa2[s][p] = __vadd2(pa2[s][p], w2);
-                                cur2[s][p] = w2;
-                            }
-                            if (DENSE && live[s]) {
-                                int32_t *o = P.dense + ((uint64_t)P.pol_index[pbase + s] * T + t0 + t + g) * P.R + r0;
-                                *reinterpret_cast<int4 *>(o) = make_int4((int32_t)(cur2[s][0] & 0xFFFFu), (int32_t)(cur2[s][0] >> 16),
-                                                                         (int32_t)(cur2[s][1] & 0xFFFFu), (int32_t)(cur2[s][1] >> 16));
-                            }
-                        }
-                    }
-                };
-                if constexpr (PACKED) {
-                    if (__all_sync(working, (uint32_t)any < kSweepPackedTallyTerm)) {
-                        run_packed();
-                        return;
-                    }
-                    // a count too large (or negative): this batch unpacked
-#pragma unroll
-                    for (int s = 0; s < SP; ++s)
-#pragma unroll
-                        for (int p = 0; p < VEC / 2; ++p) {
-                            cur[s][2 * p] = (int32_t)(cur2[s][p] & 0xFFFFu);
-                            cur[s][2 * p + 1] = (int32_t)(cur2[s][p] >> 16);
-                        }
-                }
                 // every count of the batch below 2^16 (and keys_per_pod <= 2^14): short quotient
                 // (a whole-warp choice, so that one large count does not make the warp run both forms)
                 if (MODE != kGeneric && small_kpp && __all_sync(working, (uint32_t)any < kSmallTallyTerm))

@@ -481,6 +481,11 @@ def test_short_quotient_magic_numbers_are_exact():
         assert int(m) < (1 << 32)
         q = ((t + np.uint64(1)) * m) >> np.uint64(32)
         assert (q == t // np.uint64(k)).all(), k
+        if k >= 2:
+            # quotient_up: the round-up magic number m + 1 = ceil(2^32 / k) needs no + 1 on the
+            # dividend and is exact on the same range (k = 1 has no 32-bit round-up number)
+            assert int(m) + 1 < (1 << 32)
+            assert (((t * (m + np.uint64(1))) >> np.uint64(32)) == t // np.uint64(k)).all(), k
     k = 1 << 14
     m = ((1 << 32) + k - 1) // k - 1
     assert (((1 << 18) + 1) * m) >> 32 != (1 << 18) // k
