@@ -329,8 +329,10 @@ def replay_one(queue_names, llen_trace, policies, inprog=None, current_pods=0,
     a = np.asarray(llen_trace)
     if a.ndim != 2 or a.shape[1] != len(queue_names):
         raise ValueError('llen_trace must be [T][%d]' % len(queue_names))
-    return replay_fleet(a, policies, inprog=inprog,
-                        group_off=np.array([0, len(queue_names)], dtype=np.uint64),
+    # (a scaler with ONE queue is a single-queue resource: no groups, so that a long trace can be
+    # replayed tick-parallel)
+    groups = None if len(queue_names) == 1 else np.array([0, len(queue_names)], dtype=np.uint64)
+    return replay_fleet(a, policies, inprog=inprog, group_off=groups,
                         cur0=np.array([current_pods], dtype=np.int64), want_dense=want_dense,
                         resource_type=resource_type, startup_delay=startup_delay,
                         patch_fail=None if patch_fail is None else np.asarray(patch_fail).reshape(-1, 1))

@@ -13,7 +13,7 @@ CSRC = os.path.join(HERE, 'csrc')
 LIBDIR = os.path.join(HERE, 'lib')
 OUT = os.path.join(LIBDIR, 'libkas.so')
 SOURCES = ['kas_match.cu', 'kas_replay.cu', 'kas_events.cu', 'kas_glob.cu', 'kas_ingest.cu', 'kas_comm.cu', 'kas_rdb.cu']
-HEADERS = ['kas_common.cuh', 'kas_table.h', 'kas_decide.cuh', os.path.join('..', '..', 'include', 'kas.h')]
+HEADERS = ['kas_common.cuh', 'kas_table.h', 'kas_decide.cuh', 'kas_replay_scan.cuh', os.path.join('..', '..', 'include', 'kas.h')]
 NVCC = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
 FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
          '-Xcompiler', '-fPIC,-fvisibility=hidden,-Wall', '-Xptxas', '-v',

@@ -19,6 +19,8 @@
 //   replay_grouped_tiled_kernel   multi-queue resources, the block's run of queues staged in
 //   replay_grouped_kernel         shared memory; the plain one also models the start-up delay
 //   replay_small_kernel           few resources: a warp per resource, lanes are policies
+//   replay_scan_kernel            few single-queue resources, long trace: the ticks in parallel
+//                                 (kas_replay_scan.cuh)
 //   decide_kernel, synth_trace_kernel
 #include "kas_common.cuh"
 #include "kas_decide.cuh"
@@ -514,7 +516,7 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 #ifndef KAS_SWEEP_FMA_ADDS
-#define KAS_SWEEP_FMA_ADDS 0   // packed form: patch / pod-tick sums of a tile as IMAD instead of VIADD.16x2
+#define KAS_SWEEP_FMA_ADDS 1   // packed form, uint16 trace: patch / pod-tick sums of a tile as IMAD instead of VIADD.16x2
 #endif
 #ifndef KAS_SWEEP_TMA
 #define KAS_SWEEP_TMA 1   // stage tiles with bulk asynchronous copies (TMA, cp.async.bulk + mbarrier); 0: cp.async
@@ -744,14 +746,16 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
                             for (int p = 0; p < VEC / 2; ++p) {
                                 const uint32_t c2 = cur2[s][p];
                                 const uint32_t w2 = __vimax3_s16x2(__vminu2(q2[g][p], mx2[s]), mn2[s], c2 & km2[p]);   // :255-259
-#if KAS_SWEEP_FMA_ADDS
-                                // the two sums of the tile as multiply-adds (no carry crosses the halves)
-                                np2[s][p] = __vminu2(w2 ^ c2, 0x00010001u) * (uint32_t)one + np2[s][p];             // :227
-                                pa2[s][p] = w2 * (uint32_t)one + pa2[s][p];
-#else
-                                np2[s][p] = __vadd2(np2[s][p], __vminu2(w2 ^ c2, 0x00010001u));                     // :227
-                                pa2[s][p] = __vadd2(pa2[s][p], w2);
-#endif
+                                if constexpr (KAS_SWEEP_FMA_ADDS && sizeof(E) == 2) {
+                                    // the two sums of the tile as multiply-adds (no carry crosses the halves):
+                                    // with a uint16 trace the FMA pipe has room (28.9 against 30.2 ms), with an
+                                    // int32 trace it makes no difference (26.6 / 26.4 ms)
+                                    np2[s][p] = __vminu2(w2 ^ c2, 0x00010001u) * (uint32_t)one + np2[s][p];         // :227
+                                    pa2[s][p] = w2 * (uint32_t)one + pa2[s][p];
+                                } else {
+                                    np2[s][p] = __vadd2(np2[s][p], __vminu2(w2 ^ c2, 0x00010001u));                 // :227
+                                    pa2[s][p] = __vadd2(pa2[s][p], w2);
+                                }
                                 cur2[s][p] = w2;
                             }
                             if (DENSE && live[s]) {
@@ -1627,6 +1631,10 @@ replay_grouped_sorted_kernel(const __grid_constant__ ReplayParams P) {
     }
 }
 
+}  // namespace kas
+#include "kas_replay_scan.cuh"
+namespace kas {
+
 template <typename E, int VEC, int SP>
 static void launch_identity(const ReplayParams &P, int mode, cudaStream_t stream) {
     const uint64_t threads = (P.R + VEC - 1) / VEC;
@@ -1787,6 +1795,10 @@ static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream)
     const bool delayed = a->startup_delay != 0;     // the availability model lives in the grouped kernel
     const bool small = !delayed && a->n_resources <= kSmallMaxResources &&
                        (identity || a->n_queues <= (uint64_t)kSmallTileElems);
+    // ... and when each of them owns ONE queue and the trace is long, the ticks themselves are
+    // replayed in parallel (kas_replay_scan.cuh)
+    const bool scan = small && identity && mode != kGeneric && !a->d_patch_fail &&
+                      a->n_ticks >= kScanReplayMinTicks;
     // Slots of a launch in the caller's order, except under a sweep of single-queue
     // resources: there policies are grouped by what a warp's two policies can share
     // (keys_per_pod -> the quotient; min > 0 and max > 0 -> the keep factor), and a group
@@ -1842,7 +1854,9 @@ static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream)
             P.pol[s] = d;
             P.pol_index[s] = (uint16_t)idx;
         }
-        if (small) {
+        if (scan) {
+            replay_scan_kernel<E><<<(unsigned)(P.R * P.pol_count), kScanReplayThreads, 0, stream>>>(P);
+        } else if (small) {
             launch_small<E>(P, mode, stream);
         } else if (identity && !a->d_patch_fail && !delayed) {
             if (P.pol_count == 1) {

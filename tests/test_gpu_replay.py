@@ -658,3 +658,52 @@ def test_first_pod_latency_fleets_vs_oracle(shape, delay, ipmode):
                                          cur0=cur0.astype(np.int32), patch_fail=fail, startup_delay=delay)
     rep = autoscaler.replay.sweep_report(res, first_pod=got)
     assert rep[1]['bursts_served'] == got[1]['n_served'] and rep[1]['mean_wait_seconds'] == got[1]['mean_wait'] * 5
+
+
+@pytest.mark.parametrize('R', [1, 3, 50])
+@pytest.mark.parametrize('T', [1024, 5000, 10007])
+@pytest.mark.parametrize('dtype', ['int32', 'uint16'])
+@pytest.mark.parametrize('ipmode', [0, 1, 2])
+def test_tick_parallel_replay_of_single_queue_resources(R, T, dtype, ipmode):
+    """Few single-queue resources with a long trace: the ticks are replayed in parallel (each
+    tick is a clamp of the current pods; clamps compose).  Against the sequential oracle: sane
+    policies incl. min_pods > 0 and max_pods = 0, negative and huge counts, negative and large
+    cur0, dense output, thread runs that end exactly at T."""
+    import autoscaler
+    from oracle import coracle
+    rng = np.random.default_rng(stable_seed('scan', R, T, dtype, ipmode))
+    hi = 2 ** 16 - 1 if dtype == 'uint16' else 2 ** 31 - 1
+    llen = rng.integers(0, 30, size=(T, R)).astype(np.int64)
+    llen[rng.random((T, R)) < 0.6] = 0
+    llen[rng.random((T, R)) < 0.01] = hi
+    if dtype == 'int32':
+        llen[rng.random((T, R)) < 0.02] = -rng.integers(1, 2 ** 31)
+    np_t = np.uint16 if dtype == 'uint16' else np.int32
+    inprog = ip_dev = None
+    if ipmode == 1:
+        inprog = rng.integers(-2, 4, size=R).astype(np.int64)
+        ip_dev = inprog.astype(np.int32)
+    elif ipmode == 2:
+        inprog = (rng.integers(0, 5, size=(T, R)) * (rng.random((T, R)) < 0.2)).astype(np.int64)
+        ip_dev = inprog.astype(np_t)
+    cur0 = rng.integers(-3, 40, size=R).astype(np.int32)
+    cur0[0] = 2 ** 31 - 1
+    pols = [(1, 0, 1), (3, 0, 8), (2, 1, 5), (7, 0, 0), (1, -4, 6), (16384, 2, 2), (5, 0, 2 ** 31 - 1)]
+    want = coracle.replay(llen.astype(np.int32), None if inprog is None else inprog.astype(np.int32), None,
+                          cur0, pols, want_dense=True)
+    got = autoscaler.replay.replay_fleet(llen.astype(np_t), pols, inprog=ip_dev, cur0=cur0, want_dense=True)
+    assert (got.dense == want['dense']).all()
+    assert (got.pod_ticks == want['pod_ticks']).all()
+    assert (got.n_patches == want['n_patches']).all()
+    assert (got.final == want['final']).all()
+    assert (got.sums[:, 0] == want['pod_ticks'].sum(0)).all() and (got.sums[:, 1] == want['n_patches'].sum(0)).all()
+    assert (got.sums[:, 2] == want['final'].astype(np.int64).sum(0)).all()
+    got2 = autoscaler.replay.replay_fleet(llen.astype(np_t), pols[:2], inprog=ip_dev)      # no cur0, no dense
+    want2 = coracle.replay(llen.astype(np.int32), None if inprog is None else inprog.astype(np.int32), None,
+                           None, pols[:2])
+    assert (got2.pod_ticks == want2['pod_ticks']).all() and (got2.n_patches == want2['n_patches']).all()
+    # one resource through the Autoscaler front (a single-queue scaler)
+    scaler = autoscaler.Autoscaler(None, 'predict')
+    one = scaler.replay(llen[:, :1].astype(np_t), pols[:3], current_pods=int(cur0[0]))
+    w1 = coracle.replay(llen[:, :1].astype(np.int32), None, None, cur0[:1], pols[:3])
+    assert (one.pod_ticks == w1['pod_ticks']).all() and (one.final == w1['final']).all()
