@@ -301,6 +301,8 @@ class Ctx(object):
         if self.world > 1:
             dist.init_process_group('nccl', device_id=self.dev)
             self.comm = engine.Comm.from_torch_group()       # libkas's own NCCL communicator
+            # one SM for the all-reduce that runs beside the next step's match kernel
+            engine.set_reserved_sms(int(os.environ.get('KAS_BENCH_RESERVED_SMS', 1)))
         self.peak, self.peak_src = measured_peak()
         self.args = args
 
@@ -432,16 +434,17 @@ def tally_leg(cx, cfg, headline, sampler):
     torch.cuda.synchronize()
 
     # ---- the step: K1 (+ the all-reduce on a second stream, double-buffered counts) ----------
-    counts = [torch.empty(N_PREFIX, dtype=torch.int64, device=dev) for _ in range(2)]
+    NB = 3                                    # count buffers in rotation
+    counts = [torch.empty(N_PREFIX, dtype=torch.int64, device=dev) for _ in range(NB)]
     comm_stream = torch.cuda.Stream(device=dev) if world > 1 else None
-    filled = [torch.cuda.Event() for _ in range(2)]
-    reduced = [torch.cuda.Event() for _ in range(2)]
+    filled = [torch.cuda.Event() for _ in range(NB)]
+    reduced = [torch.cuda.Event() for _ in range(NB)]
     main = torch.cuda.current_stream(dev)
 
     def step(i):
-        b = i & 1
+        b = i % NB
         if world > 1:
-            main.wait_event(reduced[b])          # the all-reduce of step i-2 has read this buffer
+            main.wait_event(reduced[b])          # the all-reduce of step i-NB is done with this buffer
         engine.match_count(d_heads, n, W, table, N_PREFIX, d_counts=counts[b], accumulate=False)
         if world > 1:
             filled[b].record(main)
@@ -462,7 +465,7 @@ def tally_leg(cx, cfg, headline, sampler):
         if i == warmup + steps - 1 or i == warmup - 1:
             drain()
     ms = cx.timed(timed_step, steps, warmup, sampler if headline else None)
-    last = (warmup + steps - 1) & 1
+    last = (warmup + steps - 1) % NB
     counts_box = engine.counts_to_host(counts[last]).astype(np.int64)
     out.update({'ms_per_step': ms, 'value': world * n / (ms * 1e-3), 'steps': steps, 'warmup': warmup,
                 'launches_per_step': 1})
@@ -963,7 +966,8 @@ def run_ours(args):
             'e2e': tally['e2e'] if keys_headline else rep['e2e'],
             'gpu_launches': head['steps'], 'clocks': clocks,
             'collective': ('one ncclAllReduce(int64 sum) per step, issued by libkas (kas_allreduce_i64) on a second '
-                           'stream, overlapped with the next step; drained inside the timed region')
+                           'stream, overlapped with the next step (the match kernel leaves %s SM free for it); '
+                           'drained inside the timed region' % os.environ.get('KAS_BENCH_RESERVED_SMS', 1))
                           if cx.world > 1 else 'none',
             'checks': {'host_affinity': cx.numa},
         }

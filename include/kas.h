@@ -16,7 +16,8 @@
  *   - the CALLER owns every device buffer ("d_" prefix) and every host buffer;
  *     the library allocates no device memory.  Its only global mutable state is
  *     a per-thread copy of the last CUDA error string, a per-thread cache of the
- *     current device's SM count, and -- for kas_patch_event_offsets_static
+ *     current device's SM count, the kas_set_reserved_sms setting, the NCCL
+ *     communicators of kas_comm_init, and -- for kas_patch_event_offsets_static
  *     alone -- one fixed 64 KB device array per GPU plus the per-device cache of
  *     its address (see that entry point for the sharing rules).
  *   - all device work is enqueued on the given stream and is asynchronous with
@@ -64,6 +65,12 @@ KAS_API int kas_version(void);
 KAS_API const char *kas_strerror(int status);
 /* Text of the last CUDA error seen by the calling thread ("" if none). */
 KAS_API const char *kas_last_cuda_error(void);
+/* Leave n SMs (0..64, default 0) out of the persistent grid of kas_match_count, process-wide.
+ * The match kernel otherwise holds every SM for its whole run, so a small kernel on another
+ * stream -- the all-reduce of the previous step's counts -- can only start in the gap between two
+ * launches and delays the next one by its own latency.  With one SM set aside the collective runs
+ * beside the match kernel (cost: 1/148 of its throughput).  No counterpart in the reference. */
+KAS_API int kas_set_reserved_sms(int n);
 /* SM count and compute capability of the current device. */
 KAS_API int kas_device_info(int *sm_count, int *cc_major, int *cc_minor);
 

@@ -96,6 +96,7 @@ SYMBOLS = {
     'kas_strerror': (C.c_char_p, [C.c_int]),
     'kas_last_cuda_error': (C.c_char_p, []),
     'kas_device_info': (C.c_int, [C.POINTER(C.c_int)] * 3),
+    'kas_set_reserved_sms': (C.c_int, [C.c_int]),
     'kas_rec_bytes_for': (C.c_uint32, [C.c_uint32]),
     'kas_pack_heads_host': (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32,
                                       C.c_void_p, C.c_int]),
@@ -518,6 +519,11 @@ def pack_heads_device(d_blob, d_off, n_keys, rec_bytes, sep_bytes=0):
     check(lib().kas_pack_heads(ptr(d_blob), ptr(d_off), n_keys, sep_bytes, rec_bytes, ptr(heads),
                                stream_ptr()), 'kas_pack_heads')
     return heads
+
+
+def set_reserved_sms(n):
+    """Leave ``n`` SMs out of the match kernel's persistent grid (room for a concurrent collective)."""
+    check(lib().kas_set_reserved_sms(int(n)), 'kas_set_reserved_sms')
 
 
 def device_info():

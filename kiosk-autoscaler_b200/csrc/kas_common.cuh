@@ -20,6 +20,8 @@ void set_text_error(const char *where, const char *what);   // same slot, for no
 
 // SM count of the current device (cached per device by the caller's thread).
 int sm_count();
+// SMs the persistent kernels leave free (kas_set_reserved_sms; 0 by default).
+int reserved_sms();
 
 static inline bool aligned(const void *p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
 

@@ -80,10 +80,17 @@ __device__ __forceinline__ bool glob_element(const uint8_t *p, uint32_t plen, ui
     return e == c;
 }
 
+// `lit`: length of the pattern's leading run of plain bytes (nothing of * ? [ \).  That run can
+// only match the same bytes at the start of the key, so it is compared in a tight loop first --
+// most (key, pattern) pairs end there -- and the general walk starts behind it.
 template <bool SHARED>
-__device__ bool glob_match(const uint8_t *p, uint32_t plen, const uint8_t *s, uint32_t saddr, uint64_t slen) {
-    uint32_t pi = 0, star_pi = 0xFFFFFFFFu;
-    uint64_t si = 0, star_si = 0;
+__device__ bool glob_match(const uint8_t *p, uint32_t plen, uint32_t lit, const uint8_t *s, uint32_t saddr,
+                           uint64_t slen) {
+    if (slen < lit) return false;
+    for (uint32_t i = 0; i < lit; ++i)
+        if (key_byte<SHARED>(s, saddr, i) != p[i]) return false;
+    uint32_t pi = lit, star_pi = 0xFFFFFFFFu;
+    uint64_t si = lit, star_si = 0;
     while (si < slen) {
         if (pi < plen && p[pi] == '*') {
             while (pi + 1 < plen && p[pi + 1] == '*') ++pi;
@@ -115,20 +122,32 @@ glob_count_kernel(const uint8_t *__restrict__ blob, const uint64_t *__restrict__
                   const uint32_t *__restrict__ pat_off, uint32_t n_patterns,
                   unsigned long long *__restrict__ counts) {
     extern __shared__ uint8_t gsm[];
-    // [n_patterns+1] offsets, [n_patterns] histogram, then the pattern bytes
+    // [n_patterns+1] offsets, [n_patterns] histogram, [n_patterns] literal-prefix lengths, then the pattern bytes
     uint32_t *s_off = reinterpret_cast<uint32_t *>(gsm);
     uint32_t *s_hist = s_off + n_patterns + 1;
-    uint8_t *s_pat = reinterpret_cast<uint8_t *>(s_hist + n_patterns);
+    uint32_t *s_lit = s_hist + n_patterns;
+    uint8_t *s_pat = reinterpret_cast<uint8_t *>(s_lit + n_patterns);
     for (uint32_t i = threadIdx.x; i <= n_patterns; i += blockDim.x) s_off[i] = pat_off[i];
     for (uint32_t i = threadIdx.x; i < n_patterns; i += blockDim.x) s_hist[i] = 0u;
     __syncthreads();
     const uint32_t total = s_off[n_patterns];
     for (uint32_t i = threadIdx.x; i < total; i += blockDim.x) s_pat[i] = patterns[i];
     __syncthreads();
+    for (uint32_t q = threadIdx.x; q < n_patterns; q += blockDim.x) {
+        const uint32_t pa = s_off[q], pl = s_off[q + 1] - pa;
+        uint32_t n = 0;
+        while (n < pl) {
+            const uint8_t c = s_pat[pa + n];
+            if (c == '*' || c == '?' || c == '[' || c == '\\') break;
+            ++n;
+        }
+        s_lit[q] = n;
+    }
+    __syncthreads();
 
     const uint32_t lane = threadIdx.x & 31u;
     // the staging area: 16-byte aligned, behind the pattern bytes
-    uint8_t *s_keys = gsm + (((2 * n_patterns + 1) * 4 + total + 15u) & ~15u);
+    uint8_t *s_keys = gsm + (((3 * n_patterns + 1) * 4 + total + 15u) & ~15u);
     const uint32_t s_keys_addr = (uint32_t)__cvta_generic_to_shared(s_keys);
     for (uint64_t base = (uint64_t)blockIdx.x * blockDim.x; base < n_keys; base += (uint64_t)gridDim.x * blockDim.x) {
         const uint64_t i = base + threadIdx.x;
@@ -154,8 +173,9 @@ glob_count_kernel(const uint8_t *__restrict__ blob, const uint64_t *__restrict__
         const uint32_t my = s_keys_addr + (uint32_t)(reinterpret_cast<uintptr_t>(blob) + a - g0);
         for (uint32_t q = 0; q < n_patterns; ++q) {       // warp-uniform loop
             const uint32_t pa = s_off[q], pl = s_off[q + 1] - pa;
-            const bool m = live && (staged ? glob_match<true>(s_pat + pa, pl, nullptr, my, len)
-                                           : glob_match<false>(s_pat + pa, pl, blob + a, 0u, len));
+            const uint32_t lit = s_lit[q];
+            const bool m = live && (staged ? glob_match<true>(s_pat + pa, pl, lit, nullptr, my, len)
+                                           : glob_match<false>(s_pat + pa, pl, lit, blob + a, 0u, len));
             const uint32_t votes = __ballot_sync(0xFFFFFFFFu, m);
             if (lane == 0 && votes) atomicAdd(&s_hist[q], (uint32_t)__popc(votes));
         }
@@ -186,7 +206,7 @@ int kas_glob_count(const uint8_t *d_blob, const uint64_t *d_off, uint64_t n_keys
     if (n_keys == 0) return KAS_OK;
     const int sms = sm_count();
     if (sms <= 0) return KAS_ERR_CUDA;
-    const size_t smem = (((2 * (size_t)n_patterns + 1) * sizeof(uint32_t) + pattern_bytes + 15) & ~(size_t)15) +
+    const size_t smem = (((3 * (size_t)n_patterns + 1) * sizeof(uint32_t) + pattern_bytes + 15) & ~(size_t)15) +
                         kGlobStageBytes;
     KAS_CUDA_TRY(cudaFuncSetAttribute(glob_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     uint64_t grid = (n_keys + kGlobThreads - 1) / kGlobThreads;

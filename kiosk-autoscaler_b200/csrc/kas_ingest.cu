@@ -9,6 +9,7 @@
 
 #include <string.h>
 #include <algorithm>
+#include <atomic>
 #include <string>
 #include <thread>
 #include <vector>
@@ -25,6 +26,9 @@ void set_cuda_error(cudaError_t e, const char *where) {
 void set_text_error(const char *where, const char *what) {
     snprintf(g_cuda_error, sizeof(g_cuda_error), "%s: %s", where, what);
 }
+
+static std::atomic<int> g_reserved_sms{0};
+int reserved_sms() { return g_reserved_sms.load(std::memory_order_relaxed); }
 
 int sm_count() {
     static thread_local int cached_dev = -1;
@@ -164,6 +168,12 @@ const char *kas_strerror(int status) {
 }
 
 const char *kas_last_cuda_error(void) { return g_cuda_error; }
+
+int kas_set_reserved_sms(int n) {
+    if (n < 0 || n > 64) return KAS_ERR_INVALID;
+    g_reserved_sms.store(n, std::memory_order_relaxed);
+    return KAS_OK;
+}
 
 int kas_device_info(int *sms, int *cc_major, int *cc_minor) {
     int dev = 0;

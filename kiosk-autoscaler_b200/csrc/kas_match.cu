@@ -513,7 +513,10 @@ static int launch_match(const void *d_heads, uint64_t n_keys, const void *d_tbl,
     if (sms <= 0) return KAS_ERR_CUDA;
     const uint64_t tile = (uint64_t)MatchCfg<NCHUNK>::kThreads * MatchCfg<NCHUNK>::kKeysPerThread;
     uint64_t want = (n_keys + tile - 1) / tile;
-    uint64_t grid = (uint64_t)sms * per_sm;
+    // persistent grid over the SMs, minus those the caller set aside (kas_set_reserved_sms) so that
+    // a kernel on another stream -- the all-reduce of the previous step -- finds room beside it
+    const int free_sms = sms - reserved_sms() > 0 ? sms - reserved_sms() : 1;
+    uint64_t grid = (uint64_t)free_sms * per_sm;
     if (want < grid) grid = want;
     if (grid == 0) grid = 1;
     kern<<<(unsigned)grid, MatchCfg<NCHUNK>::kThreads, smem, stream>>>(

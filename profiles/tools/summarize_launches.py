@@ -4,8 +4,11 @@ import collections
 import csv
 import sys
 
-HEAD = """ncu launch list of `python bench.py --steps 20 --warmup 3 --no-cpu` (B200, round 1; cold-cache serialised times: compare shares).
-The timed region of the bench is the 20 match_count launches of the step loop; the other launches are warm-up, the end-to-end leg (12 chunk launches per step), the 16M-key checks and the replay leg (int32 and uint16 traces).
+HEAD = """ncu launch list of `python bench.py --steps 20 --warmup 5 --no-cpu --no-extras` (B200; `ncu --metrics
+gpu__time_duration.sum --clock-control none`, first 600 launches; cold-cache serialised times: compare shares, not
+absolutes).  The timed region of the bench is the 20 match_count launches of the step loop (one launch per step);
+the other launches are warm-up, the oracle slice check, the end-to-end legs (12 chunk launches per step; the raw
+form adds one pack_heads launch per chunk), and the replay leg (default policy, sweep, int32 and uint16 traces).
 """
 
 
