@@ -757,6 +757,24 @@ def replay_leg(cx, cfg, headline, sampler):
                   'sample': 'the first %d ticks of the fleet (a %d-byte pinned host trace per rank): the step is '
                             'the H2D copy, so the rate does not depend on the tick count' % (T_e, Q * T_e * 4),
                   'path': 'autoscaler.replay.replay_fleet(pinned int32 host trace) -> H2D -> kas_replay -> sums D2H'}
+    # the same from a uint16 host trace (half the bytes over PCIe)
+    if int(htrace.max().item()) < 32768:
+        h16 = htrace.to(torch.int16).pin_memory()
+
+        def e2e16_once():
+            got['sums16'] = kreplay.replay_fleet(h16, [DEFAULT_POLICY], group_off=go, want_totals=False).sums
+        e2e16_once()
+        cx.barrier()
+        w0 = time.perf_counter()
+        for _ in range(reps):
+            e2e16_once()
+        e16_ms = cx.max_over_ranks((time.perf_counter() - w0) * 1e3 / reps)
+        if not cx.all_true(bool((got['sums16'] == want_sums).all())):
+            raise SystemExit('bench.py: end-to-end uint16 replay sums differ from the resident-trace sums')
+        rep['e2e_uint16'] = {'value': world * Q * T_e / (e16_ms * 1e-3), 'unit': '(queue,tick) decisions/s',
+                             'h2d_bytes_per_step': Q * T_e * 2, 'd2h_bytes_per_step': 24, 'ms_per_step': e16_ms,
+                             'h2d_gbs_per_rank': Q * T_e * 2 / (e16_ms * 1e-3) / 1e9, 'matches_resident_result': True}
+        del h16
     del htrace
 
     # ---- CPU baseline: the oracle's scale() loop on a slice of the same trace ----------------
@@ -905,6 +923,26 @@ def extras_leg(cx, cfg, tally):
                        'roofline': cx.roofline('replay_grouped_sorted_kernel', Qg * Tg * esz, ms1, 'replay_grouped_sorted_kernel')}
         del o, tot
     out['multi_queue_fleet'] = {'queues': Qg, 'resources': R, 'ticks': Tg, 'group_sizes': '1-8', **grouped}
+    # the `only_running` reading under a pod start-up delay of three ticks (autoscaler.py:176-177): the
+    # plain kernel with a window of the last specs per thread, element-wise loads
+    delay = {}
+    for label, dgo, dR in (('single_queue', None, Qg), ('multi_queue', d_go, R)):
+        msd = time_ms(lambda: engine.replay(trace, Tg, Qg, [DEFAULT_POLICY], d_group_off=dgo, n_resources=dR,
+                                            want_totals=False, startup_delay=3), reps=5)
+        od = engine.replay(trace, Tg, Qg, [DEFAULT_POLICY], d_group_off=dgo, n_resources=dR, startup_delay=3)
+        td = engine.totals_to_host(od['totals'])
+        for r in (1, dR // 2):
+            q0, q1 = (r, r + 1) if dgo is None else (int(go[r]), int(go[r + 1]))
+            w = coracle.replay(coracle.trace_fill(3, Tg, q0, q1 - q0), None,
+                               None if dgo is None else np.array([0, q1 - q0], dtype=np.uint64), None,
+                               [DEFAULT_POLICY], startup_delay=3)
+            if td['pod_ticks'][r].tolist() != w['pod_ticks'][0].tolist() or \
+                    td['n_patches'][r].tolist() != w['n_patches'][0].tolist():
+                raise SystemExit('bench.py: start-up-delay replay differs from the oracle')
+        delay[label] = {'ms': msd, 'queue_ticks_per_sec': Qg * Tg / (msd * 1e-3), 'oracle_equal_on_samples': True,
+                        'roofline': cx.roofline('replay_grouped_kernel<DELAY>', Qg * Tg * 4, msd)}
+        del od, td
+    out['startup_delay_3_ticks'] = {'queues': Qg, 'ticks': Tg, **delay}
     del trace, d_go
 
     # the reference's own case: ONE resource, QUEUES='predict,track', 10k ticks, the 41-policy sweep

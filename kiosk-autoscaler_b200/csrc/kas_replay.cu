@@ -1799,6 +1799,11 @@ static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream)
     // replayed in parallel (kas_replay_scan.cuh)
     const bool scan = small && identity && mode != kGeneric && !a->d_patch_fail &&
                       a->n_ticks >= kScanReplayMinTicks;
+    // ... any other small fleet with a long trace: the few possible states are enumerated
+    // (it multiplies the work by the number of states to divide the depth by 256: only worth it
+    // while resources x policies cannot fill the machine with sequential chains)
+    const bool fsm = small && !scan && a->n_ticks >= kScanReplayMinTicks &&
+                     a->n_resources * (uint64_t)a->n_policies <= 2048;
     // Slots of a launch in the caller's order, except under a sweep of single-queue
     // resources: there policies are grouped by what a warp's two policies can share
     // (keys_per_pod -> the quotient; min > 0 and max > 0 -> the keep factor), and a group
@@ -1856,6 +1861,10 @@ static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream)
         }
         if (scan) {
             replay_scan_kernel<E><<<(unsigned)(P.R * P.pol_count), kScanReplayThreads, 0, stream>>>(P);
+        } else if (fsm) {
+            const size_t smem = (size_t)kFsmThreads * 256;
+            KAS_CUDA_TRY(cudaFuncSetAttribute(replay_fsm_kernel<E>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            replay_fsm_kernel<E><<<(unsigned)(P.R * P.pol_count), kFsmThreads, smem, stream>>>(P);
         } else if (small) {
             launch_small<E>(P, mode, stream);
         } else if (identity && !a->d_patch_fail && !delayed) {

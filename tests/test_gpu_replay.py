@@ -707,3 +707,53 @@ def test_tick_parallel_replay_of_single_queue_resources(R, T, dtype, ipmode):
     one = scaler.replay(llen[:, :1].astype(np_t), pols[:3], current_pods=int(cur0[0]))
     w1 = coracle.replay(llen[:, :1].astype(np.int32), None, None, cur0[:1], pols[:3])
     assert (one.pod_ticks == w1['pod_ticks']).all() and (one.final == w1['final']).all()
+
+
+@pytest.mark.parametrize('shape', ['two_queues', 'mixed_groups', 'single_queue_failing'])
+@pytest.mark.parametrize('dtype', ['int32', 'uint16'])
+@pytest.mark.parametrize('ipmode', [0, 1, 2])
+def test_small_fleet_long_trace_by_state_enumeration(shape, dtype, ipmode):
+    """A few resources with a long trace and small max_pods: every possible pod count is pushed
+    through runs of ticks in parallel and the runs are chained (kas_replay_scan.cuh).  Multi-queue
+    resources, failing patch calls, a starting count outside [0, max_pods], and blocks that do
+    not fit the form (min_pods < 0, max_pods > 254, nine queues) against the sequential oracle."""
+    import autoscaler
+    from oracle import coracle
+    rng = np.random.default_rng(stable_seed('fsm', shape, dtype, ipmode))
+    T = 3001
+    sizes = {'two_queues': [2], 'mixed_groups': [1, 3, 8, 9, 2], 'single_queue_failing': [1, 1, 1]}[shape]
+    go = np.concatenate([[0], np.cumsum(sizes)]).astype(np.uint64)
+    Q, R = int(go[-1]), len(sizes)
+    hi = 2 ** 16 - 1 if dtype == 'uint16' else 2 ** 31 - 1
+    llen = rng.integers(0, 12, size=(T, Q)).astype(np.int64)
+    llen[rng.random((T, Q)) < 0.7] = 0
+    llen[rng.random((T, Q)) < 0.003] = hi
+    if dtype == 'int32':
+        llen[rng.random((T, Q)) < 0.01] = -rng.integers(1, 1000)
+    np_t = np.uint16 if dtype == 'uint16' else np.int32
+    inprog = ip_dev = None
+    if ipmode == 1:
+        inprog = rng.integers(0, 3, size=Q).astype(np.int64)
+        ip_dev = inprog.astype(np.int32)
+    elif ipmode == 2:
+        inprog = (rng.integers(0, 5, size=(T, Q)) * (rng.random((T, Q)) < 0.1)).astype(np.int64)
+        ip_dev = inprog.astype(np_t)
+    cur0 = rng.integers(0, 5, size=R).astype(np.int32)
+    cur0[0] = 2 ** 31 - 1
+    if R > 1:
+        cur0[1] = -7
+    fail = rng.random((T, R)) < 0.2
+    pols = [(1, 0, 1), (2, 0, 4), (1, 1, 16), (5, 0, 64), (1, 0, 254), (1, 0, 255), (3, -2, 6), (-2, 0, 5),
+            (7, 0, 0), (1, 3, 3), (2, 0, 1000)]
+    want = coracle.replay(llen.astype(np.int32), None if inprog is None else inprog.astype(np.int32), go, cur0, pols,
+                          want_dense=True, patch_fail=fail)
+    got = autoscaler.replay.replay_fleet(llen.astype(np_t), pols, inprog=ip_dev, group_off=go, cur0=cur0,
+                                         want_dense=True, patch_fail=fail)
+    assert (got.dense == want['dense']).all()
+    assert (got.pod_ticks == want['pod_ticks']).all()
+    assert (got.n_patches == want['n_patches']).all()
+    assert (got.final == want['final']).all()
+    assert (got.sums[:, 0] == want['pod_ticks'].sum(0)).all() and (got.sums[:, 1] == want['n_patches'].sum(0)).all()
+    got2 = autoscaler.replay.replay_fleet(llen.astype(np_t), pols[:4], inprog=ip_dev, group_off=go)
+    want2 = coracle.replay(llen.astype(np.int32), None if inprog is None else inprog.astype(np.int32), go, None, pols[:4])
+    assert (got2.pod_ticks == want2['pod_ticks']).all() and (got2.final == want2['final']).all()
