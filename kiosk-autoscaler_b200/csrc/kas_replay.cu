@@ -430,22 +430,48 @@ replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
     if (valid) {
         const uint64_t q0 = P.group_off ? P.group_off[r] : r;
         const uint64_t q1 = P.group_off ? P.group_off[r + 1] : r + 1;
+        // a resource with ONE queue (and this kernel's extras: the start-up delay, failing patches):
+        // the loads of the next ticks do not depend on the state, so eight ticks are fetched at
+        // once instead of one load per tick at the head of the dependency chain
+        constexpr uint32_t kAhead = 8;
+        const bool single = q1 - q0 == 1;
+        int32_t lbuf[kAhead], ibuf[kAhead];
+        const int32_t *iq = static_cast<const int32_t *>(P.inprog);                  // per-queue term
         for (uint32_t t = 0; t < T; ++t) {
             const E *lrow = static_cast<const E *>(P.llen) + (uint64_t)t * Q;
             const E *irow = static_cast<const E *>(P.inprog) + (uint64_t)t * Q;      // per-tick term
-            const int32_t *iq = static_cast<const int32_t *>(P.inprog);              // per-queue term
             const bool failed = P.patch_fail && P.patch_fail[(uint64_t)t * P.R + r];
             long long sum[SP];
 #pragma unroll
             for (int s = 0; s < SP; ++s) sum[s] = 0;
-            for (uint64_t q = q0; q < q1; ++q) {
-                const int32_t l = ld_trace_cached<E>(lrow + q);
-                const int32_t ip = P.inprog_mode == 2 ? ld_trace_cached<E>(irow + q)
-                                                      : (P.inprog_mode == 1 ? __ldg(iq + q) : 0);
+            if (single) {
+                if (t % kAhead == 0) {
+#pragma unroll
+                    for (uint32_t u = 0; u < kAhead; ++u) {
+                        const uint32_t tt = min(t + u, T - 1);
+                        lbuf[u] = ld_trace<E>(static_cast<const E *>(P.llen) + (uint64_t)tt * Q + q0);
+                        ibuf[u] = P.inprog_mode == 2 ? ld_trace<E>(static_cast<const E *>(P.inprog) + (uint64_t)tt * Q + q0)
+                                                     : (P.inprog_mode == 1 ? __ldg(iq + q0) : 0);
+                    }
+                }
+                int32_t l = lbuf[0], ip = ibuf[0];
+#pragma unroll
+                for (uint32_t u = 1; u < kAhead; ++u)
+                    if (t % kAhead == u) { l = lbuf[u]; ip = ibuf[u]; }
 #pragma unroll
                 for (int s = 0; s < SP; ++s)
                     if (pbase + s < P.pol_count)
                         sum[s] += decide<MODE>(l, ip, P.pol[pbase + s], cur[s]);   // :255-257
+            } else {
+                for (uint64_t q = q0; q < q1; ++q) {
+                    const int32_t l = ld_trace_cached<E>(lrow + q);
+                    const int32_t ip = P.inprog_mode == 2 ? ld_trace_cached<E>(irow + q)
+                                                          : (P.inprog_mode == 1 ? __ldg(iq + q) : 0);
+#pragma unroll
+                    for (int s = 0; s < SP; ++s)
+                        if (pbase + s < P.pol_count)
+                            sum[s] += decide<MODE>(l, ip, P.pol[pbase + s], cur[s]);   // :255-257
+                }
             }
 #pragma unroll
             for (int s = 0; s < SP; ++s) {
@@ -815,6 +841,8 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
                                 big |= (uint32_t)(b.x | b.y | b.z | b.w);
                                 x[g][0] += (uint32_t)b.x; x[g][1] += (uint32_t)b.y; x[g][2] += (uint32_t)b.z; x[g][3] += (uint32_t)b.w;
                             } else {
+                                // (zero without a per-queue term; skipping the adds under a uniform
+                                // branch measured 9 % slower)
 #pragma unroll
                                 for (int v = 0; v < VEC; ++v) x[g][v] += (uint32_t)ipq[v];
                             }
