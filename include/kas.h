@@ -37,7 +37,7 @@
 extern "C" {
 #endif
 
-#define KAS_VERSION 102 /* 0.1.2: kas_comm_*, kas_allreduce_i64 */
+#define KAS_VERSION 103 /* 0.1.3: kas_replay_args.d_resume, kas_totals_chain */
 
 #if defined(__GNUC__)
 #define KAS_API __attribute__((visibility("default")))
@@ -266,6 +266,15 @@ typedef struct kas_replay_args {
                                    Outputs stay spec.replicas after the tick.  Only
                                    deployments have this reading (a job always reports
                                    spec.parallelism, :185-190): pass 0 for jobs.       */
+    const kas_totals *d_resume; /* NULL, or the d_totals [R][S] of an earlier replay of
+                                   the SAME resources and policy list: every (resource,
+                                   policy) starts from that entry's final_current
+                                   instead of d_cur0 (which must then be NULL).  This
+                                   is how a trace longer than HBM is replayed in
+                                   chunks of ticks: chunk k+1 resumes from chunk k's
+                                   totals and kas_totals_chain adds them up.  Not with
+                                   startup_delay (the availability window is not part
+                                   of the totals); must not alias d_totals.            */
 } kas_replay_args;
 #define KAS_MAX_STARTUP_DELAY 16u
 
@@ -275,6 +284,16 @@ typedef struct kas_replay_args {
  * alignment and Q a multiple of 4 (int32) or 8 (uint16) enable the vectorised
  * paths for single-queue resources.                                          */
 KAS_API int kas_replay(const kas_replay_args *args, void *stream);
+
+/* Chain the totals of consecutive tick chunks of one replay (checkpoint / resume; the
+ * reference keeps no state between ticks but what Kubernetes holds, autoscaler.py:252):
+ *   d_acc[i].pod_ticks += d_chunk[i].pod_ticks;  n_patches likewise;
+ *   d_acc[i].final_current = d_chunk[i].final_current            for i < n_resources * n_policies,
+ * and, when both are given, the same for the [S][3] sums (sums of pod_ticks and n_patches
+ * add up, the sum of final_current is the later chunk's). */
+KAS_API int kas_totals_chain(kas_totals *d_acc, const kas_totals *d_chunk, uint64_t n_resources,
+                             uint32_t n_policies, int64_t *d_sums_acc, const int64_t *d_sums_chunk,
+                             void *stream);
 
 /* ------------------------------------------------------------------------
  * Patch-event stream of a replay: the calls Autoscaler.scale_resource would

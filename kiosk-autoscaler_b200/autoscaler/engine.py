@@ -74,7 +74,7 @@ class ReplayArgs(C.Structure):
                 ('policies', C.POINTER(Policy)), ('n_policies', C.c_uint32),
                 ('d_totals', C.c_void_p), ('d_sums', C.c_void_p), ('d_dense', C.c_void_p),
                 ('trace_dtype', C.c_int32), ('d_patch_fail', C.c_void_p),
-                ('startup_delay', C.c_uint32)]
+                ('startup_delay', C.c_uint32), ('d_resume', C.c_void_p)]
 
 
 MAX_STARTUP_DELAY = 16      # KAS_MAX_STARTUP_DELAY
@@ -126,6 +126,7 @@ SYMBOLS = {
                                                  C.c_void_p]),
     'kas_patch_event_emit': (C.c_int, [C.POINTER(ReplayArgs), C.c_uint32, C.c_void_p, C.c_void_p,
                                        C.c_uint64, C.c_void_p]),
+    'kas_totals_chain': (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
     'kas_first_pod_latency': (C.c_int, [C.POINTER(ReplayArgs), C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
     'kas_comm_unique_id': (C.c_int, [C.c_void_p]),
     'kas_comm_init': (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_void_p]),
@@ -403,10 +404,13 @@ def trace_dtype_of(t):
 
 def replay(d_llen, n_ticks, n_queues, policies, d_inprog=None, inprog_mode=0, d_group_off=None,
            n_resources=None, d_cur0=None, want_totals=True, want_sums=True, want_dense=False,
-           d_patch_fail=None, startup_delay=0):
+           d_patch_fail=None, startup_delay=0, d_resume=None, out_totals=None, out_sums=None):
     """K2 on device tensors.  policies: sequence of (kpp, min, max).
     ``startup_delay`` > 0: the controller reads the AVAILABLE replicas of a deployment
     (the reference's ``only_running`` branch) under the start-up model of include/kas.h.
+    ``d_resume``: the totals tensor of an earlier replay of the same fleet and policies; every
+    (resource, policy) starts from its final pods (chunked replay, see ``totals_chain``).
+    ``out_totals`` / ``out_sums``: tensors to write into instead of fresh ones.
     The trace may be int32 or uint16 (a per-tick in-progress trace has the same type).
     Returns dict of CUDA tensors: totals (uint8 view [R][S][16]), sums int64 [S][3],
     dense int32 [S][T][R] (those requested)."""
@@ -421,15 +425,19 @@ def replay(d_llen, n_ticks, n_queues, policies, d_inprog=None, inprog_mode=0, d_
     parr = (Policy * S)(*[Policy(*p) for p in pol])
     dev = d_llen.device
     out = {}
-    totals = torch.empty((R, S, 16), dtype=torch.uint8, device=dev) if want_totals else None
-    sums = torch.empty((S, 3), dtype=torch.int64, device=dev) if want_sums else None
+    totals = (out_totals if out_totals is not None
+              else torch.empty((R, S, 16), dtype=torch.uint8, device=dev)) if want_totals else None
+    sums = (out_sums if out_sums is not None
+            else torch.empty((S, 3), dtype=torch.int64, device=dev)) if want_sums else None
+    if d_resume is not None and tuple(d_resume.shape) != (R, S, 16):
+        raise ValueError('d_resume must be the totals [R][S] of an earlier replay of the same fleet and policies')
     dense = torch.empty((S, n_ticks, R), dtype=torch.int32, device=dev) if want_dense else None
     dt = trace_dtype_of(d_llen)
     if inprog_mode == 2 and trace_dtype_of(d_inprog) != dt:
         raise TypeError('a per-tick in-progress trace must have the element type of the LLEN trace')
     args = ReplayArgs(ptr(d_llen), ptr(d_inprog), inprog_mode, n_ticks, n_queues, R,
                       ptr(d_group_off), ptr(d_cur0), parr, S, ptr(totals), ptr(sums), ptr(dense), dt,
-                      ptr(d_patch_fail), _check_delay(startup_delay))
+                      ptr(d_patch_fail), _check_delay(startup_delay), ptr(d_resume))
     check(lib().kas_replay(C.byref(args), stream_ptr()), 'kas_replay')
     if want_totals:
         out['totals'] = totals
@@ -457,7 +465,7 @@ def patch_events(d_llen, n_ticks, n_queues, policy, d_inprog=None, inprog_mode=0
         raise TypeError('a per-tick in-progress trace must have the element type of the LLEN trace')
     args = ReplayArgs(ptr(d_llen), ptr(d_inprog), inprog_mode, n_ticks, n_queues, R,
                       ptr(d_group_off), ptr(d_cur0), parr, 1, None, None, None, dt, ptr(d_patch_fail),
-                      _check_delay(startup_delay))
+                      _check_delay(startup_delay), None)
     off = torch.empty(R + 1, dtype=torch.int64, device=dev)
     nscratch = lib().kas_patch_events_scratch_bytes(R)
     scratch = torch.empty(max(nscratch, 8), dtype=torch.uint8, device=dev)
@@ -489,13 +497,20 @@ def first_pod_latency(d_llen, n_ticks, n_queues, policy, d_inprog=None, inprog_m
         raise TypeError('a per-tick in-progress trace must have the element type of the LLEN trace')
     args = ReplayArgs(ptr(d_llen), ptr(d_inprog), inprog_mode, n_ticks, n_queues, R,
                       ptr(d_group_off), ptr(d_cur0), parr, 1, None, None, None, dt, ptr(d_patch_fail),
-                      _check_delay(startup_delay))
+                      _check_delay(startup_delay), None)
     rows = torch.empty((R, FIRST_POD_DTYPE.itemsize), dtype=torch.uint8, device=dev) if want_rows else None
     sums = torch.empty(5, dtype=torch.int64, device=dev)
     check(lib().kas_first_pod_latency(C.byref(args), 0, ptr(rows), ptr(sums), stream_ptr()),
           'kas_first_pod_latency')
     host_rows = rows.cpu().numpy().reshape(-1).view(FIRST_POD_DTYPE) if want_rows else None
     return host_rows, sums.cpu().numpy()
+
+
+def totals_chain(d_acc, d_chunk, d_sums_acc=None, d_sums_chunk=None):
+    """acc += chunk for the totals (and sums) of consecutive tick chunks (kas_totals_chain)."""
+    R, S = int(d_acc.shape[0]), int(d_acc.shape[1])
+    check(lib().kas_totals_chain(ptr(d_acc), ptr(d_chunk), R, S, ptr(d_sums_acc), ptr(d_sums_chunk),
+                                 stream_ptr()), 'kas_totals_chain')
 
 
 def totals_to_host(d_totals):

@@ -320,6 +320,105 @@ def _allreduce_first_pod(sums, comm):
     return np.array([v[0], v[1], v[2], v[4:].max(), v[3]], dtype=np.int64)
 
 
+class StreamingReplay(object):
+    """Replay a trace that sits in host memory -- or is longer than the GPU's memory -- in chunks
+    of ticks.  The scale loop keeps no state between ticks but the pods Kubernetes holds
+    (autoscaler.py:252 of the reference), so a chunk only needs the final pods of the chunk before
+    it: chunk k+1 resumes from chunk k's totals (``kas_replay_args.d_resume``) and
+    ``kas_totals_chain`` adds the totals up.  Chunks are copied into two device staging buffers
+    on a copy stream while the previous chunk is replayed; the result is, bit for bit, that of
+    one replay of the whole trace.  (A start-up delay cannot be chunked: its availability window
+    is not part of the totals.)"""
+
+    def __init__(self, policies, n_queues, group_off=None, chunk_ticks=512, trace_dtype='int32',
+                 per_tick_inprog=False, device='cuda'):
+        torch = engine.require_cuda()
+        self.policies = [tuple(int(v) for v in p) for p in policies]
+        self.Q = int(n_queues)
+        self.device = torch.device(device)
+        self.chunk_ticks = int(chunk_ticks)
+        self.d_go, self.R = None, self.Q
+        if group_off is not None:
+            go = np.ascontiguousarray(group_off, dtype=np.uint64)
+            if go[0] != 0 or go[-1] != self.Q or (np.diff(go.astype(np.int64)) < 0).any():
+                raise ValueError('group_off must rise from 0 to Q')
+            self.R = len(go) - 1
+            self.d_go = torch.from_numpy(go.view(np.int64)).to(self.device)
+        self.tdtype = torch.int16 if trace_dtype in ('uint16', np.uint16) else torch.int32
+        S = len(self.policies)
+        n_stage = 2 if not per_tick_inprog else 4
+        self.stage = [torch.empty((self.chunk_ticks, self.Q), dtype=self.tdtype, device=self.device)
+                      for _ in range(n_stage)]
+        self.free = [torch.cuda.Event() for _ in range(2)]
+        self.copy_stream = torch.cuda.Stream(device=self.device)
+        self.acc = torch.empty((self.R, S, 16), dtype=torch.uint8, device=self.device)
+        self.tmp = torch.empty((self.R, S, 16), dtype=torch.uint8, device=self.device)
+        self.sums_acc = torch.empty((S, 3), dtype=torch.int64, device=self.device)
+        self.sums_tmp = torch.empty((S, 3), dtype=torch.int64, device=self.device)
+        self.per_tick_inprog = per_tick_inprog
+        self.chunks = 0
+
+    def _host(self, x, what):
+        torch = engine.require_cuda()
+        if x is None:
+            return None
+        if not isinstance(x, torch.Tensor):
+            a = np.ascontiguousarray(x)
+            if self.tdtype == torch.int16:
+                if a.size and (a.min() < 0 or a.max() > 65535):
+                    raise OverflowError('%s does not fit the uint16 trace format' % what)
+                a = a.astype(np.uint16).view(np.int16)
+            else:
+                a = a.astype(np.int32, copy=False)
+            x = torch.from_numpy(a)
+        if x.dtype == torch.uint16:
+            x = x.view(torch.int16)
+        if x.dtype != self.tdtype or x.dim() != 2 or x.shape[1] != self.Q:
+            raise TypeError('%s must be [T][%d] of the streaming replay\'s trace type' % (what, self.Q))
+        return x.contiguous()
+
+    def run(self, host_trace, inprog=None, cur0=None):
+        """host_trace: [T][Q] numpy array or CPU tensor (pinned for asynchronous copies).
+        inprog: None, per-queue int32 [Q], or -- with per_tick_inprog -- a second [T][Q] host trace.
+        cur0: pods before the first tick, int32 [R].  Returns a ``ReplayResult``."""
+        torch = engine.require_cuda()
+        llen = self._host(host_trace, 'host_trace')
+        T = int(llen.shape[0])
+        tick_ip = self._host(inprog, 'inprog') if self.per_tick_inprog else None
+        d_ipq = None if self.per_tick_inprog else _to_device_i32(inprog, torch, 'inprog')
+        d_c0 = _to_device_i32(cur0, torch, 'cur0')
+        main = torch.cuda.current_stream(self.device)
+        for b in range(2):
+            self.free[b].record(main)
+        for k, t0 in enumerate(range(0, T, self.chunk_ticks)):
+            nt = min(self.chunk_ticks, T - t0)
+            b = k & 1
+            with torch.cuda.stream(self.copy_stream):
+                self.copy_stream.wait_event(self.free[b])
+                self.stage[b][:nt].copy_(llen[t0:t0 + nt], non_blocking=True)
+                if tick_ip is not None:
+                    self.stage[2 + b][:nt].copy_(tick_ip[t0:t0 + nt], non_blocking=True)
+                ready = torch.cuda.Event()
+                ready.record(self.copy_stream)
+            main.wait_event(ready)
+            first = k == 0
+            engine.replay(self.stage[b][:nt], nt, self.Q, self.policies,
+                          d_inprog=self.stage[2 + b][:nt] if tick_ip is not None else d_ipq,
+                          inprog_mode=2 if tick_ip is not None else (0 if d_ipq is None else 1),
+                          d_group_off=self.d_go, n_resources=self.R,
+                          d_cur0=d_c0 if first else None, d_resume=None if first else self.acc,
+                          out_totals=self.acc if first else self.tmp,
+                          out_sums=self.sums_acc if first else self.sums_tmp)
+            if not first:
+                engine.totals_chain(self.acc, self.tmp, self.sums_acc, self.sums_tmp)
+            self.free[b].record(main)
+            self.chunks += 1
+        res = ReplayResult(self.policies, totals=engine.totals_to_host(self.acc),
+                           sums=self.sums_acc.cpu().numpy(), n_ticks=T)
+        res._bodies_from_dense = False
+        return res
+
+
 def replay_one(queue_names, llen_trace, policies, inprog=None, current_pods=0,
                resource_type='deployment', managed=('deployment', 'job'), want_dense=False,
                patch_fail=None, startup_delay=0):

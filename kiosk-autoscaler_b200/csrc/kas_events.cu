@@ -27,7 +27,8 @@ struct EventParams {
     const void *llen;       // trace elements: int32 or uint16 (template type E)
     const void *inprog;     // per-tick term: same type; per-queue term: int32 [Q]
     const uint64_t *group_off;
-    const int32_t *cur0;
+    const int32_t *cur0;             // pods before tick 0 of resource r: cur0[r * cur0_stride]
+    uint64_t cur0_stride;            // 1, or 4 * S when it points into the kas_totals [R][S] of a resumed replay
     const uint8_t *patch_fail;       // [T][R] or null
     unsigned long long *event_off;   // [R+1]; counts live in [1..R] between the steps
     kas_patch_event *events;
@@ -49,7 +50,7 @@ events_kernel(const __grid_constant__ EventParams P) {
     const PolDev pol = P.pol;
     const uint64_t q0 = P.group_off ? P.group_off[r] : r;
     const uint64_t q1 = P.group_off ? P.group_off[r + 1] : r + 1;
-    int32_t cur = P.cur0 ? P.cur0[r] : 0;     // what the controller reads
+    int32_t cur = P.cur0 ? P.cur0[r * P.cur0_stride] : 0;     // what the controller reads
     int32_t spec = cur;                       // what was last patched (differs under startup_delay)
     const uint32_t D = P.startup_delay;
     SpecWindow win;
@@ -104,7 +105,7 @@ first_pod_kernel(const __grid_constant__ EventParams P, kas_first_pod *__restric
         const PolDev pol = P.pol;
         const uint64_t q0 = P.group_off ? P.group_off[r] : r;
         const uint64_t q1 = P.group_off ? P.group_off[r + 1] : r + 1;
-        int32_t cur = P.cur0 ? P.cur0[r] : 0;     // what the controller reads
+        int32_t cur = P.cur0 ? P.cur0[r * P.cur0_stride] : 0;     // what the controller reads
         int32_t spec = cur;
         const uint32_t D = P.startup_delay;
         SpecWindow win;
@@ -299,6 +300,13 @@ static int fill_event_params(const kas_replay_args *a, uint32_t policy_index, Ev
     P.inprog = a->d_inprog;
     P.group_off = a->d_group_off;
     P.cur0 = a->d_cur0;
+    P.cur0_stride = 1;
+    if (a->d_resume) {
+        if (a->d_cur0 || a->startup_delay) return KAS_ERR_INVALID;
+        if (!aligned(a->d_resume, 8)) return KAS_ERR_ALIGNMENT;
+        P.cur0 = reinterpret_cast<const int32_t *>(a->d_resume) + 3 + 4ull * policy_index;   // .final_current
+        P.cur0_stride = 4ull * a->n_policies;
+    }
     P.patch_fail = a->d_patch_fail;
     P.Q = a->n_queues;
     P.R = a->n_resources;

@@ -40,7 +40,9 @@ struct ReplayParams {
     const void *llen;       // trace elements: int32 or uint16 (the kernels' template type E)
     const void *inprog;     // per-tick term: same element type; per-queue term: int32 [Q]
     const uint64_t *group_off;
-    const int32_t *cur0;
+    const int32_t *cur0;         // pods before tick 0: element (r, policy) at cur0[r * cur0_rstride + policy * cur0_sstride]
+    uint32_t cur0_rstride;       // 1 / 0 for the caller's [R] array; 4 * S / 4 when it points into a kas_totals [R][S]
+    uint32_t cur0_sstride;       //   array whose final_current fields a resumed replay starts from
     const uint8_t *patch_fail;   // [T][R] or null: the patch call of (tick, resource) raises and is swallowed
     kas_totals *totals;
     unsigned long long *sums;
@@ -56,6 +58,13 @@ struct ReplayParams {
     uint16_t pol_index[kMaxPoliciesPerLaunch];   // slot -> index of the policy in the caller's list
     PolDev pol[kMaxPoliciesPerLaunch];
 };
+
+// Pods of resource r before the first tick under the policy in slot `slot` of this launch.
+__device__ __forceinline__ int32_t initial_pods(const ReplayParams &P, uint64_t r, uint32_t slot) {
+    if (!P.cur0) return 0;
+    const uint32_t idx = P.pol_index[slot] == 0xFFFFu ? 0u : P.pol_index[slot];      // an empty slot is never written out
+    return P.cur0[r * P.cur0_rstride + (uint64_t)idx * P.cur0_sstride];
+}
 
 // n += (a != b) as a compare and a predicated add (two instructions).
 __device__ __forceinline__ void count_if_ne(uint32_t &n, int32_t a, int32_t b) {
@@ -124,10 +133,12 @@ replay_identity_kernel(const __grid_constant__ ReplayParams P) {
     int32_t ipq[VEC];
 #pragma unroll
     for (int v = 0; v < VEC; ++v) {
-        const int32_t c0 = (valid && P.cur0) ? P.cur0[r0 + v] : 0;
         ipq[v] = (valid && IPMODE == 1) ? static_cast<const int32_t *>(P.inprog)[r0 + v] : 0;
 #pragma unroll
-        for (int s = 0; s < SP; ++s) { cur[s][v] = c0; pt[s][v] = 0; np[s][v] = 0u; }
+        for (int s = 0; s < SP; ++s) {
+            cur[s][v] = (valid && live[s]) ? initial_pods(P, r0 + v, pbase + s) : 0;
+            pt[s][v] = 0; np[s][v] = 0u;
+        }
     }
 
     if (valid) {
@@ -415,7 +426,6 @@ replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
     int32_t cur[SP];
     long long pt[SP];
     uint32_t np[SP];
-    const int32_t c0 = (valid && P.cur0) ? P.cur0[r] : 0;
     // DELAY (startup_delay > 0): cur[] is what the controller reads, the AVAILABLE replicas
     // (autoscaler.py:176-177); spec[] is what was last patched; win[] the specs of the last
     // D ticks.  Without it the two are the same number.
@@ -424,6 +434,7 @@ replay_grouped_kernel(const __grid_constant__ ReplayParams P) {
     SpecWindow win[DELAY ? SP : 1];
 #pragma unroll
     for (int s = 0; s < SP; ++s) {
+        const int32_t c0 = (valid && pbase + s < P.pol_count) ? initial_pods(P, r, pbase + s) : 0;
         cur[s] = c0; spec[s] = c0; pt[s] = 0; np[s] = 0u;
         if constexpr (DELAY) win[s].init(c0, D);
     }
@@ -626,10 +637,12 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
     int32_t ipq[VEC];
 #pragma unroll
     for (int v = 0; v < VEC; ++v) {
-        const int32_t c0 = (valid && P.cur0) ? P.cur0[r0 + v] : 0;
         ipq[v] = (valid && P.inprog_mode == 1) ? static_cast<const int32_t *>(P.inprog)[r0 + v] : 0;
 #pragma unroll
-        for (int s = 0; s < SP; ++s) { cur[s][v] = c0; pt[s][v] = 0; np[s][v] = 0u; }
+        for (int s = 0; s < SP; ++s) {
+            cur[s][v] = (valid && live[s]) ? initial_pods(P, r0 + v, pbase + s) : 0;
+            pt[s][v] = 0; np[s][v] = 0u;
+        }
     }
     int32_t ipq_sign = 0;     // negative when a per-queue in-progress count is
 #pragma unroll
@@ -1038,7 +1051,7 @@ replay_small_kernel(const __grid_constant__ ReplayParams P) {
     const uint32_t nq = (uint32_t)((P.group_off ? P.group_off[r + 1] : r + 1) - q0);
     const uint32_t T = P.T;
     const uint32_t tile_ticks = nq ? kSmallTileElems / nq : T;
-    int32_t cur = P.cur0 ? P.cur0[r] : 0;
+    int32_t cur = live ? initial_pods(P, r, lane) : 0;
     long long pt = 0;
     uint32_t np = 0;
     for (uint32_t t0 = 0; t0 < T; t0 += tile_ticks) {
@@ -1118,6 +1131,27 @@ decide_kernel(const long long *__restrict__ a, const long long *__restrict__ kpp
     }
 }
 
+// ---- totals of consecutive tick chunks (resume) ------------------------------
+__global__ void __launch_bounds__(256)
+totals_chain_kernel(kas_totals *__restrict__ acc, const kas_totals *__restrict__ chunk, uint64_t n,
+                    long long *__restrict__ sums_acc, const long long *__restrict__ sums_chunk, uint32_t S) {
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        kas_totals a = acc[i];
+        const kas_totals c = chunk[i];
+        a.pod_ticks += c.pod_ticks;
+        a.n_patches += c.n_patches;
+        a.final_current = c.final_current;
+        acc[i] = a;
+    }
+    if (sums_acc && blockIdx.x == 0 && threadIdx.x < S) {
+        long long *a = sums_acc + 3 * threadIdx.x;
+        const long long *c = sums_chunk + 3 * threadIdx.x;
+        a[0] += c[0];
+        a[1] += c[1];
+        a[2] = c[2];
+    }
+}
+
 // ---- synthetic trace (spec in DESIGN.md; twin in oracle/kas_oracle.c) ------
 __device__ __forceinline__ uint64_t mix64(uint64_t z) {
     z += 0x9E3779B97F4A7C15ULL;
@@ -1187,9 +1221,11 @@ replay_grouped_tiled_kernel(const __grid_constant__ ReplayParams P) {
     int32_t cur[SP];
     long long pt[SP];
     uint32_t np[SP];
-    const int32_t c0 = (valid && P.cur0) ? P.cur0[r] : 0;
 #pragma unroll
-    for (int s = 0; s < SP; ++s) { cur[s] = c0; pt[s] = 0; np[s] = 0u; }
+    for (int s = 0; s < SP; ++s) {
+        cur[s] = (valid && pbase + s < P.pol_count) ? initial_pods(P, r, pbase + s) : 0;
+        pt[s] = 0; np[s] = 0u;
+    }
     const uint64_t q0 = valid ? P.group_off[r] : 0, q1 = valid ? P.group_off[r + 1] : 0;
     // The staged run covers this block's queues only if the offsets do not go back or leave
     // [0, Q]; a block that sees such offsets reads element by element, like the plain kernel.
@@ -1863,6 +1899,13 @@ static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream)
         P.inprog = a->d_inprog;
         P.group_off = a->d_group_off;
         P.cur0 = a->d_cur0;
+        P.cur0_rstride = 1;
+        P.cur0_sstride = 0;
+        if (a->d_resume) {       // start from the final pods of an earlier replay's totals [R][S]
+            P.cur0 = reinterpret_cast<const int32_t *>(a->d_resume) + 3;      // kas_totals.final_current
+            P.cur0_rstride = 4 * a->n_policies;
+            P.cur0_sstride = 4;
+        }
         P.patch_fail = a->d_patch_fail;
         P.totals = a->d_totals;
         P.sums = reinterpret_cast<unsigned long long *>(a->d_sums);
@@ -1899,7 +1942,7 @@ static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream)
             if (P.pol_count == 1) {
                 const PolDev &pd = P.pol[0];
                 const bool packable = sizeof(E) == 2 && vec && mode != kGeneric && a->inprog_mode == 0 &&
-                                      !a->d_cur0 && pd.mn >= 0 && pd.mx <= kPackedMaxPods && pd.m32 != 0u;
+                                      !P.cur0 && pd.mn >= 0 && pd.mx <= kPackedMaxPods && pd.m32 != 0u;
                 if (packable) {
                     const unsigned grid = (unsigned)((P.R / 8 + kReplayThreads - 1) / kReplayThreads);
                     if (pd.k1) replay_packed16_kernel<true><<<grid, kReplayThreads, 0, stream>>>(P);
@@ -1936,6 +1979,10 @@ int kas_replay(const kas_replay_args *a, void *stream_v) {
     if (a->startup_delay > KAS_MAX_STARTUP_DELAY) return KAS_ERR_INVALID;
     if (!a->d_group_off && a->n_resources != a->n_queues) return KAS_ERR_INVALID;
     if (!a->d_totals && !a->d_sums && !a->d_dense) return KAS_ERR_INVALID;
+    if (a->d_resume && (a->d_cur0 || a->startup_delay)) return KAS_ERR_INVALID;   // one source of starting pods; the
+                                                                                   // availability window is not carried
+    if (a->d_resume && a->d_resume == a->d_totals) return KAS_ERR_INVALID;        // read while being written
+    if (!aligned(a->d_resume, 8)) return KAS_ERR_ALIGNMENT;
     if (a->n_resources > (0x7FFFFFFFull / kMaxPoliciesPerLaunch) * kReplayThreads) return KAS_ERR_UNSUPPORTED;
     const size_t elem = a->trace_dtype == KAS_TRACE_UINT16 ? 2 : 4;
     if (!aligned(a->d_llen, elem) || !aligned(a->d_inprog, a->inprog_mode == 2 ? elem : 4) ||
@@ -1949,6 +1996,26 @@ int kas_replay(const kas_replay_args *a, void *stream_v) {
         KAS_CUDA_TRY(cudaMemsetAsync(a->d_sums, 0, sizeof(int64_t) * 3 * a->n_policies, stream));
     return a->trace_dtype == KAS_TRACE_UINT16 ? replay_typed<uint16_t>(a, mode, stream)
                                               : replay_typed<int32_t>(a, mode, stream);
+}
+
+int kas_totals_chain(kas_totals *d_acc, const kas_totals *d_chunk, uint64_t n_resources, uint32_t n_policies,
+                     int64_t *d_sums_acc, const int64_t *d_sums_chunk, void *stream_v) {
+    if (!d_acc || !d_chunk || n_policies == 0 || (d_sums_acc != nullptr) != (d_sums_chunk != nullptr))
+        return KAS_ERR_INVALID;
+    if (n_policies > 256 && d_sums_acc) return KAS_ERR_UNSUPPORTED;
+    if (!aligned(d_acc, 8) || !aligned(d_chunk, 8) || !aligned(d_sums_acc, 8) || !aligned(d_sums_chunk, 8))
+        return KAS_ERR_ALIGNMENT;
+    const uint64_t n = n_resources * n_policies;
+    if (n == 0) return KAS_OK;
+    const int sms = sm_count();
+    if (sms <= 0) return KAS_ERR_CUDA;
+    uint64_t grid = (n + 255) / 256;
+    if (grid > (uint64_t)sms * 16) grid = (uint64_t)sms * 16;
+    totals_chain_kernel<<<(unsigned)grid, 256, 0, static_cast<cudaStream_t>(stream_v)>>>(
+        d_acc, d_chunk, n, reinterpret_cast<long long *>(d_sums_acc),
+        reinterpret_cast<const long long *>(d_sums_chunk), n_policies);
+    KAS_CUDA_TRY(cudaGetLastError());
+    return KAS_OK;
 }
 
 int kas_decide(const int64_t *d_a, const int64_t *d_kpp, const int64_t *d_mn, const int64_t *d_mx,

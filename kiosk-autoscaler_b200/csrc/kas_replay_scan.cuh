@@ -99,7 +99,7 @@ replay_scan_kernel(const __grid_constant__ ReplayParams P) {
         if (lane > 0) before = clamp_then(before, prev);
     }
     // 3. replay the run from the state before it
-    const int32_t c0 = P.cur0 ? P.cur0[r] : 0;
+    const int32_t c0 = initial_pods(P, r, slot);
     int32_t cur = clamp_apply(before, c0);
     long long pt = 0;
     uint32_t np = 0;
@@ -175,7 +175,7 @@ replay_fsm_kernel(const __grid_constant__ ReplayParams P) {
     const uint64_t q0 = P.group_off ? P.group_off[r] : r;
     const uint64_t q1 = P.group_off ? P.group_off[r + 1] : r + 1;
     const uint32_t nq = q1 > q0 ? (uint32_t)min(q1 - q0, (uint64_t)0xFFFFFFFFu) : 0u;
-    const int32_t c0 = P.cur0 ? P.cur0[r] : 0;
+    const int32_t c0 = initial_pods(P, r, slot);
     const bool fits = pol.mn >= 0 && pol.mx <= kFsmMaxPods && pol.mn <= pol.mx && nq <= kFsmMaxQueues &&
                       q1 - q0 <= kFsmMaxQueues;
     // the targets of one tick (autoscaler.py:200-203 per queue; exact for any count) ...

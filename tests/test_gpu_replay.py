@@ -757,3 +757,68 @@ def test_small_fleet_long_trace_by_state_enumeration(shape, dtype, ipmode):
     got2 = autoscaler.replay.replay_fleet(llen.astype(np_t), pols[:4], inprog=ip_dev, group_off=go)
     want2 = coracle.replay(llen.astype(np.int32), None if inprog is None else inprog.astype(np.int32), go, None, pols[:4])
     assert (got2.pod_ticks == want2['pod_ticks']).all() and (got2.final == want2['final']).all()
+
+
+@pytest.mark.parametrize('shape', ['identity', 'grouped', 'small'])
+@pytest.mark.parametrize('dtype', ['int32', 'uint16'])
+@pytest.mark.parametrize('ipmode', [0, 1, 2])
+def test_chunked_replay_resumes_bit_for_bit(shape, dtype, ipmode):
+    """A trace replayed in chunks of ticks (each chunk resumes from the totals of the one before,
+    kas_replay_args.d_resume + kas_totals_chain) gives the integers of one replay of the whole
+    trace and of the oracle: streamed from host memory, several policies, cur0 on the first chunk,
+    chunk sizes that do not divide T; and the patch log of a resumed chunk continues the log."""
+    import torch
+    import autoscaler
+    from autoscaler import engine
+    from oracle import coracle
+    rng = np.random.default_rng(stable_seed('resume', shape, dtype, ipmode))
+    T, Q = {'identity': (333, 8192), 'grouped': (257, 6000), 'small': (1500, 24)}[shape]
+    llen, go = helpers.random_fleet(rng, T, Q, grouped=(shape != 'identity'))
+    R = Q if go is None else len(go) - 1
+    np_t = np.uint16 if dtype == 'uint16' else np.int32
+    inprog = ip_dev = None
+    if ipmode == 1:
+        inprog = rng.integers(0, 4, size=Q).astype(np.int32)
+        ip_dev = inprog
+    elif ipmode == 2:
+        inprog = (rng.integers(0, 6, size=(T, Q)) * (rng.random((T, Q)) < 0.2)).astype(np.int32)
+        ip_dev = inprog.astype(np_t)
+    cur0 = rng.integers(0, 9, size=R).astype(np.int32)
+    pols = [(1, 0, 1), (3, 1, 9), (5, 0, 64), (2, 0, 4), (-2, 0, 6), (1, 7, 3)]
+    want = coracle.replay(llen, inprog, go, cur0, pols)
+    for chunk in (64, 100, T):
+        sr = autoscaler.replay.StreamingReplay(pols, Q, group_off=go, chunk_ticks=chunk, trace_dtype=dtype,
+                                               per_tick_inprog=(ipmode == 2))
+        host = torch.from_numpy(llen.astype(np_t).view(np.int16) if dtype == 'uint16' else llen).pin_memory()
+        got = sr.run(host, inprog=ip_dev, cur0=cur0)
+        assert sr.chunks == -(-T // chunk)
+        assert (got.pod_ticks == want['pod_ticks']).all()
+        assert (got.n_patches == want['n_patches']).all()
+        assert (got.final == want['final']).all()
+        assert (got.sums[:, 0] == want['pod_ticks'].sum(0)).all() and (got.sums[:, 1] == want['n_patches'].sum(0)).all()
+        assert (got.sums[:, 2] == want['final'].astype(np.int64).sum(0)).all()
+    # the patch log of the second half, resumed from the totals of the first
+    half = T // 2
+    d = torch.from_numpy(llen.astype(np_t).view(np.int16) if dtype == 'uint16' else llen).cuda()
+    d_go = None if go is None else torch.from_numpy(go.view(np.int64)).cuda()
+    d_ip = None if ip_dev is None else torch.from_numpy(ip_dev.view(np.int16) if ip_dev.dtype == np.uint16 else ip_dev).cuda()
+    first = engine.replay(d[:half], half, Q, pols, d_inprog=None if d_ip is None else (d_ip[:half] if ipmode == 2 else d_ip),
+                          inprog_mode=ipmode, d_group_off=d_go, n_resources=R, d_cur0=torch.from_numpy(cur0).cuda())
+    R_ = R
+    parr = (engine.Policy * len(pols))(*[engine.Policy(*p) for p in pols])
+    args = engine.ReplayArgs(engine.ptr(d[half:]), engine.ptr(None if d_ip is None else (d_ip[half:] if ipmode == 2 else d_ip)),
+                             ipmode, T - half, Q, R_, engine.ptr(d_go), None, parr, len(pols), None, None, None,
+                             engine.trace_dtype_of(d), None, 0, engine.ptr(first['totals']))
+    off = torch.empty(R_ + 1, dtype=torch.int64, device='cuda')
+    scratch = torch.empty(max(8, engine.lib().kas_patch_events_scratch_bytes(R_)), dtype=torch.uint8, device='cuda')
+    engine.check(engine.lib().kas_patch_event_offsets(engine.C.byref(args), 1, engine.ptr(off), engine.ptr(scratch),
+                                                      scratch.numel(), engine.stream_ptr()), 'kas_patch_event_offsets')
+    whole = coracle.replay(llen, inprog, go, cur0, [pols[1]], want_dense=True)['dense'][0]
+    before = whole[half - 1]
+    changes = ((np.diff(np.concatenate([before[None], whole[half:]]), axis=0) != 0).sum(0))
+    assert (np.diff(off.cpu().numpy()) == changes).all()
+    # arguments that cannot be combined
+    bad = engine.ReplayArgs(engine.ptr(d), None, 0, T, Q, R_, engine.ptr(d_go), engine.ptr(torch.from_numpy(cur0).cuda()),
+                            parr, len(pols), engine.ptr(first['totals']), None, None, engine.trace_dtype_of(d), None, 0,
+                            engine.ptr(first['totals']))
+    assert engine.lib().kas_replay(engine.C.byref(bad), engine.stream_ptr()) == engine.KAS_ERR_INVALID

@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(L, name), name
     assert declared == set(engine.SYMBOLS), declared ^ set(engine.SYMBOLS)
-    assert L.kas_version() == 102
+    assert L.kas_version() == 103
     assert L.kas_strerror(-5) == b'integer division or modulo by zero'
     assert L.kas_rec_bytes_for(7) == 32 and L.kas_rec_bytes_for(4) == 16 and L.kas_rec_bytes_for(21) == 48
     # struct layouts the header promises
