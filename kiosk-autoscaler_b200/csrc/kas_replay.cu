@@ -552,6 +552,11 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
+#ifndef KAS_SWEEP_KEEPALL
+#define KAS_SWEEP_KEEPALL 0    // packed form: a separate instance of the tick code for policy groups with min_pods > 0
+                               // (one ALU instruction per pair and policy less, but 27.2 against 26.4 ms for int32 and
+                               // 28.6 against 28.9 ms for uint16: the second copy of the tick code costs what it saves)
+#endif
 #ifndef KAS_SWEEP_FMA_ADDS
 #define KAS_SWEEP_FMA_ADDS 1   // packed form, uint16 trace: patch / pod-tick sums of a tile as IMAD instead of VIADD.16x2
 #endif
@@ -675,6 +680,7 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
     const uint32_t k64k = 65536u * (uint32_t)one;
     const uint32_t m_up = pol[0].m32 + 1u;      // ceil(2^32 / keys_per_pod), keys_per_pod >= 2 (see quotient_up)
     const bool kpp_one = pol[0].k1 != 0u;
+    const bool keep_all = keep.add != 0u;       // min_pods > 0 (and then max_pods > 0): the keep factor is always 1
     // per-queue in-progress counts as packed pairs, and whether they fit the packed form at all
     uint32_t ipq2[VEC / 2];
 #pragma unroll
@@ -772,38 +778,50 @@ replay_sweep_kernel(const __grid_constant__ ReplayParams P) {
                 // policies of the warp share the quotients, packed q2, and the keep factors as a mask km2
                 // (0xFFFF where keep == 1); per policy: min with max_pods, the three-input maximum with
                 // min_pods and the kept current pods, and the two sums of the tile.
+                // KEEPALL: the warp's policies have min_pods > 0, so every decision is positive and the
+                // current pods are always kept (keep factor 1): no mask to build, no AND.  (Two plain
+                // lambdas from one macro: a generic lambda with a tag parameter here crashes cicc 12.9.)
+#define KAS_RUN_PACKED(NAME, KEEPALL)                                                                                  \
+                auto NAME = [&](const uint32_t (&q2)[G][VEC / 2]) {                                                    \
+                    _Pragma("unroll")                                                                                  \
+                    for (int g = 0; g < G; ++g) {                                                                      \
+                        uint32_t km2[VEC / 2];                                                                         \
+                        _Pragma("unroll")                                                                              \
+                        for (int p = 0; p < VEC / 2; ++p)                                                              \
+                            km2[p] = KEEPALL ? 0xFFFFFFFFu : __viaddmin_u16x2(q2[g][p], add2, 0x00010001u) * 0xFFFFu;  \
+                        _Pragma("unroll")                                                                              \
+                        for (int s = 0; s < SP; ++s) {                                                                 \
+                            _Pragma("unroll")                                                                          \
+                            for (int p = 0; p < VEC / 2; ++p) {                                                        \
+                                const uint32_t c2 = cur2[s][p];                                                        \
+                                const uint32_t w2 = __vimax3_s16x2(__vminu2(q2[g][p], mx2[s]), mn2[s],                 \
+                                                                   KEEPALL ? c2 : (c2 & km2[p])); /* :255-259 */      \
+                                if constexpr (KAS_SWEEP_FMA_ADDS && sizeof(E) == 2) {                                  \
+                                    /* the two sums of the tile as multiply-adds (no carry crosses the halves): */    \
+                                    /* with a uint16 trace the FMA pipe has room (28.9 against 30.2 ms), with an */   \
+                                    /* int32 trace it makes no difference (26.6 / 26.4 ms) */                         \
+                                    np2[s][p] = __vminu2(w2 ^ c2, 0x00010001u) * (uint32_t)one + np2[s][p]; /* :227 */ \
+                                    pa2[s][p] = w2 * (uint32_t)one + pa2[s][p];                                        \
+                                } else {                                                                               \
+                                    np2[s][p] = __vadd2(np2[s][p], __vminu2(w2 ^ c2, 0x00010001u));         /* :227 */ \
+                                    pa2[s][p] = __vadd2(pa2[s][p], w2);                                                \
+                                }                                                                                      \
+                                cur2[s][p] = w2;                                                                       \
+                            }                                                                                          \
+                            if (DENSE && live[s]) {                                                                    \
+                                int32_t *o = P.dense + ((uint64_t)P.pol_index[pbase + s] * T + t0 + t + g) * P.R + r0; \
+                                *reinterpret_cast<int4 *>(o) = make_int4((int32_t)(cur2[s][0] & 0xFFFFu), (int32_t)(cur2[s][0] >> 16), \
+                                                                         (int32_t)(cur2[s][1] & 0xFFFFu), (int32_t)(cur2[s][1] >> 16)); \
+                            }                                                                                          \
+                        }                                                                                              \
+                    }                                                                                                  \
+                }
+                KAS_RUN_PACKED(run_packed_mask, false);
+                KAS_RUN_PACKED(run_packed_keep, true);
+#undef KAS_RUN_PACKED
                 auto run_packed = [&](const uint32_t (&q2)[G][VEC / 2]) {
-#pragma unroll
-                    for (int g = 0; g < G; ++g) {
-                        uint32_t km2[VEC / 2];
-#pragma unroll
-                        for (int p = 0; p < VEC / 2; ++p)
-                            km2[p] = __viaddmin_u16x2(q2[g][p], add2, 0x00010001u) * 0xFFFFu;
-#pragma unroll
-                        for (int s = 0; s < SP; ++s) {
-#pragma unroll
-                            for (int p = 0; p < VEC / 2; ++p) {
-                                const uint32_t c2 = cur2[s][p];
-                                const uint32_t w2 = __vimax3_s16x2(__vminu2(q2[g][p], mx2[s]), mn2[s], c2 & km2[p]);   // :255-259
-                                if constexpr (KAS_SWEEP_FMA_ADDS && sizeof(E) == 2) {
-                                    // the two sums of the tile as multiply-adds (no carry crosses the halves):
-                                    // with a uint16 trace the FMA pipe has room (28.9 against 30.2 ms), with an
-                                    // int32 trace it makes no difference (26.6 / 26.4 ms)
-                                    np2[s][p] = __vminu2(w2 ^ c2, 0x00010001u) * (uint32_t)one + np2[s][p];         // :227
-                                    pa2[s][p] = w2 * (uint32_t)one + pa2[s][p];
-                                } else {
-                                    np2[s][p] = __vadd2(np2[s][p], __vminu2(w2 ^ c2, 0x00010001u));                 // :227
-                                    pa2[s][p] = __vadd2(pa2[s][p], w2);
-                                }
-                                cur2[s][p] = w2;
-                            }
-                            if (DENSE && live[s]) {
-                                int32_t *o = P.dense + ((uint64_t)P.pol_index[pbase + s] * T + t0 + t + g) * P.R + r0;
-                                *reinterpret_cast<int4 *>(o) = make_int4((int32_t)(cur2[s][0] & 0xFFFFu), (int32_t)(cur2[s][0] >> 16),
-                                                                         (int32_t)(cur2[s][1] & 0xFFFFu), (int32_t)(cur2[s][1] >> 16));
-                            }
-                        }
-                    }
+                    if (KAS_SWEEP_KEEPALL && keep_all) run_packed_keep(q2);
+                    else run_packed_mask(q2);
                 };
                 if constexpr (PACKED) {
                     // The common batch -- every count below 2^14 -- never leaves the packed form: the
