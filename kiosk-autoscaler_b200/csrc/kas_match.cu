@@ -29,6 +29,9 @@ namespace kas {
 #ifndef KAS_MATCH_U
 #define KAS_MATCH_U 2      // keys per thread per step (32-byte records); two steps are in flight
 #endif
+#ifndef KAS_MATCH_U1
+#define KAS_MATCH_U1 KAS_MATCH_U   // the same for 16-byte records (half the bytes per record in flight)
+#endif
 #ifndef KAS_MATCH_MINB
 #define KAS_MATCH_MINB 1   // resident blocks per SM the register budget is held to (narrow records)
 #endif
@@ -66,7 +69,7 @@ struct MatchCfg {
     static constexpr int kRWP = (kRW + 3) / 4 * 4;                         // padded to 128-bit rows
     static constexpr int kEW = kRW + 2;                                    // entry words
     static constexpr int kRows = 16 * NCHUNK - (int)kRegionStart;           // colon positions inside the region
-    static constexpr int kKeysPerThread = NCHUNK <= 2 ? KAS_MATCH_U : 1;
+    static constexpr int kKeysPerThread = NCHUNK == 1 ? KAS_MATCH_U1 : (NCHUNK <= 2 ? KAS_MATCH_U : 1);
     static constexpr int kThreads = NCHUNK <= 2 ? KAS_MATCH_THREADS : 256;
     static constexpr int kMinBlocks = NCHUNK <= 2 ? KAS_MATCH_MINB : 3;    // wide records need the registers
     using mask_t = typename std::conditional<(kRows <= 32), uint32_t, uint64_t>::type;   // one bit per colon position

@@ -11,7 +11,9 @@ import bench  # noqa: E402
 from autoscaler import engine  # noqa: E402
 
 n = int(os.environ.get('KAS_BENCH_KEYS', 100_000_000))
-names = {'c2': bench.queue_names(), 'two': ['predict', 'track'], 'one': ['predict']}[os.environ.get('KAS_NAMES', 'c2')]
+names = {'c2': bench.queue_names(), 'two': ['predict', 'track'], 'one': ['predict'],
+         'w16': ['q%d' % i for i in range(8)],
+         'n1024': ['q%04d%s' % (i, 'abcdefghij'[:i % 11]) for i in range(1024)]}[os.environ.get('KAS_NAMES', 'c2')]
 W = engine.rec_bytes_for(names)
 host = torch.empty(n * W, dtype=torch.uint8).pin_memory()
 engine.synth_keys_host(2, 0, n, names, rec_bytes=W, heads_out=host)
