@@ -498,7 +498,13 @@ def test_startup_delay_limits_agree():
     m = re.search(r'#define\s+KAS_MAX_STARTUP_DELAY\s+(\d+)u', hdr)
     assert m and int(m.group(1)) == engine.MAX_STARTUP_DELAY
     assert 'startup_delay' in dict(engine.ReplayArgs._fields_)
-    assert engine.ReplayArgs._fields_[-1][0] == 'startup_delay'       # appended, older callers zero it
+    # optional fields are appended in the order they were added; older callers zero them
+    assert [f[0] for f in engine.ReplayArgs._fields_[-3:]] == ['d_patch_fail', 'startup_delay', 'd_resume']
+    # the struct the header declares has the same members in the same order
+    body = hdr[hdr.index('typedef struct kas_replay_args {'):hdr.index('} kas_replay_args;')]
+    body = re.sub(r'/\*.*?\*/', '', body, flags=re.S)
+    members = re.findall(r'\b(\w+)\s*;', body)
+    assert members == [f[0] for f in engine.ReplayArgs._fields_]
     with pytest.raises(ValueError):
         engine._check_delay(engine.MAX_STARTUP_DELAY + 1)
     with pytest.raises(ValueError):
