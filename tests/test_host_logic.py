@@ -470,6 +470,35 @@ def test_reference_arm_prints_one_json_line():
     assert 'workload' in d['config']
 
 
+def test_reference_arm_decisions_and_configs():
+    """--impl reference for the other metric and a multi-queue config: honours --steps/--warmup,
+    names its bounded sample in config, never loads the product library."""
+    import json
+    import subprocess
+    env = dict(os.environ, KAS_BENCH_CPU_QUEUES='300', KAS_BENCH_REPLAY_T='200')
+    for extra, metric in ((['--metric', 'decisions'], 'scaling decisions/sec'),
+                          (['--config', 'c5', '--metric', 'decisions'], 'scaling decisions/sec'),
+                          (['--config', 'c4'], 'scaling decisions/sec')):
+        out = subprocess.run([sys.executable, '-X', 'importtime', os.path.join(ROOT, 'bench.py'), '--impl', 'reference',
+                              '--steps', '3', '--warmup', '1'] + extra, capture_output=True, text=True, env=env,
+                             timeout=300)
+        assert out.returncode == 0, out.stderr[-500:]
+        lines = [ln for ln in out.stdout.splitlines() if ln.strip()]
+        assert len(lines) == 1
+        d = json.loads(lines[0])
+        assert d['impl'] == 'reference' and d['metric'] == metric and d['steps'] == 3 and d['warmup'] == 1
+        assert d['config']['cpu_sample_queues'] == 300 and 'bounded sample' in d['config']['cpu_sample']
+        assert d['e2e']['value'] == d['value'] and d['gpu_launches'] == 0
+        assert 'autoscaler.engine' not in out.stderr          # -X importtime lists every imported module
+    sys.path.insert(0, ROOT)
+    import bench
+    go = bench.fleet_groups(5, 1000, 5000)
+    assert go[0] == 0 and go[-1] == 5000 and (np.diff(go.astype(np.int64)) >= 1).all()
+    assert (np.diff(go.astype(np.int64)) <= 8).all() and (bench.fleet_groups(5, 1000, 5000) == go).all()
+    types = bench.resource_types(2, 0, 1000)
+    assert set(types) == {'job', 'deployment'} and 0.4 < (types == 'job').mean() < 0.6
+
+
 def test_short_quotient_magic_numbers_are_exact():
     """The policy-sweep kernel divides small tallies with ONE multiply-high:
     floor(t / k) == ((t + 1) * (ceil(2^32 / k) - 1)) >> 32 for every t < 2^17 and every
