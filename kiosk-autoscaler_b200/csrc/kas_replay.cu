@@ -1426,9 +1426,7 @@ constexpr uint32_t kGsStageBytesPerThread = 96;
 constexpr uint32_t kGsMaxTileTicks = 32;
 constexpr uint32_t kGsMaxOwn = 2048;          // queues of one resource: x kGsMaxPods stays below 2^31
 constexpr int32_t kGsMaxPods = 1 << 20;
-#ifndef KAS_GS_UNROLL_SP4
-#define KAS_GS_UNROLL_SP4 0    /* unroll the queue loop under four policies per thread as well (measured slower) */
-#endif
+
 constexpr uint32_t gs_stage_bytes(int threads) { return (uint32_t)threads * kGsStageBytesPerThread; }
 constexpr int gs_stages(int threads) { return threads >= 512 ? 2 : 3; }
 
@@ -1645,7 +1643,7 @@ replay_grouped_sorted_kernel(const __grid_constant__ ReplayParams P) {
                     }
                 }
             };
-            if (SP == 1 || KAS_GS_UNROLL_SP4) {
+            if (SP == 1 || (SP == 2 && sizeof(E) == 2)) {
                 switch (n_max) {
                     case 1: run_tile(std::integral_constant<int, 1>{}); break;
                     case 2: run_tile(std::integral_constant<int, 2>{}); break;
@@ -1976,8 +1974,12 @@ static int replay_typed(const kas_replay_args *a, int mode, cudaStream_t stream)
                 }
             }
         } else {
+            // several policies: four per thread over an int32 trace (fewer passes over HBM), two per
+            // thread with the queue loop unrolled over a uint16 trace (half the bytes per pass; 36.0
+            // against 51.7 ms for 41 policies x 2e9 queue-ticks; for int32 the same costs 59 against 54.5)
+            constexpr int kMultiSP = sizeof(E) == 2 ? 2 : 4;
             const int st = P.pol_count == 1 ? launch_grouped<E, 1>(P, mode, stream)
-                                            : launch_grouped<E, 4>(P, mode, stream);
+                                            : launch_grouped<E, kMultiSP>(P, mode, stream);
             if (st != KAS_OK) return st;
         }
         KAS_CUDA_TRY(cudaGetLastError());

@@ -39,7 +39,9 @@ def timed(pol, reps):
 
 m1, o1 = timed([(1, 0, 1)], 5)
 m4, o4 = timed([(1, 0, 1), (2, 0, 4), (5, 1, 16), (10, 0, 64)], 3)
+import bench  # noqa: E402
+m41, o41 = timed(bench.SWEEP, 2)
 esz = trace.element_size()
-print('grouped R=%d Q=%d T=%d %s: S=1 %.3f ms (%.0f GB/s)  S=4 %.3f ms (%.3e dec/s)  chk=%d' % (
+print('grouped R=%d Q=%d T=%d %s: S=1 %.3f ms (%.0f GB/s)  S=4 %.3f ms (%.3e dec/s)  S=41 %.2f ms (%.3e dec/s)  chk=%d/%d' % (
     R, Q, T, os.environ.get('KAS_TRACE_DTYPE', 'int32'), m1, T * Q * esz / m1 / 1e6, m4, T * Q * 4 / m4 * 1e3,
-    int(o1['sums'][0, 0])), flush=True)
+    m41, T * Q * 41 / m41 * 1e3, int(o1['sums'][0, 0]), int(o41['sums'][:, 0].sum())), flush=True)
