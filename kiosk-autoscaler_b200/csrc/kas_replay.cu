@@ -1627,6 +1627,9 @@ replay_grouped_sorted_kernel(const __grid_constant__ ReplayParams P) {
                     } else {
                         for (uint32_t j = 0; j < n_own; ++j) one_queue(j, 1u);
                     }
+                    // (checking once per tile instead -- fast code for the whole tile, then a replay of
+                    // the tile from saved state if a count was out of range -- measured 32 % slower for
+                    // one policy over int32, 1.72 against 1.30 ms: the saved state costs registers)
                     int32_t want[SP];
                     if (kCheck && any >= kSmallTallyTerm) {
                         slow_tick(lrow, irow, want);
